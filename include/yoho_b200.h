@@ -1,0 +1,179 @@
+/*
+ * yoho_b200.h -- C ABI of the B200-native YOHO hot path (log-mel frontend +
+ * Whisper audio-encoder forward).
+ *
+ * The reference (JirkaKlimes/YOHO) has no plugin / FFI interface: the boundary is four
+ * Python call signatures traced under jax.jit / jax.pmap.  Each entry point below names
+ * the reference call it stands in for (paths relative to the reference checkout); the
+ * Python mirror in yoho_b200/ keeps the reference names and binds these symbols with
+ * ctypes, and csrc/xla_ffi.cc wraps the same symbols as jax.ffi custom calls.
+ *
+ * Conventions
+ *   - plain C, no C++ types, no exceptions cross the boundary;
+ *   - every array pointer is a DEVICE pointer owned by the caller unless the name says
+ *     `host_`; all arrays are dense, row-major, C-contiguous;
+ *   - every compute call is asynchronous on the caller's stream (`yoho_stream_t` is a
+ *     `cudaStream_t`), performs no allocation and no synchronisation; scratch memory is
+ *     passed in (`ws`, size from the matching `*_workspace_bytes`);
+ *   - return value: YOHO_OK (0) or a negative yoho_status; `yoho_last_error()` returns a
+ *     thread-local message for the last failure on the calling thread;
+ *   - there is no CPU fallback: on a device that is not sm_100 every compute call fails
+ *     with YOHO_ERR_ARCH.
+ */
+#ifndef YOHO_B200_H_
+#define YOHO_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YOHO_ABI_VERSION 1
+
+typedef struct yoho_ctx yoho_ctx;               /* per-device immutable state           */
+typedef struct yoho_filterbank yoho_filterbank; /* banded mel filterbank on the device  */
+typedef void* yoho_stream_t;                    /* cudaStream_t                         */
+
+typedef enum yoho_status {
+  YOHO_OK = 0,
+  YOHO_ERR_INVALID = -1,     /* bad argument (null pointer, negative size, shape rule)  */
+  YOHO_ERR_UNSUPPORTED = -2, /* valid in the reference, not implemented by the kernels  */
+  YOHO_ERR_WORKSPACE = -3,   /* ws_bytes smaller than *_workspace_bytes()               */
+  YOHO_ERR_CUDA = -4,        /* a CUDA runtime / driver call failed                     */
+  YOHO_ERR_ARCH = -5         /* device is not compute capability 10.x                   */
+} yoho_status;
+
+typedef enum yoho_norm {
+  YOHO_NORM_NONE = 0,      /* mel power, what mel_spectogram returns (audio.py:32-37)        */
+  YOHO_NORM_REFERENCE = 1, /* normalize_spectogram: log10(max(x,1e-13)), (x-mean)/std (audio.py:53-58) */
+  YOHO_NORM_WHISPER = 2    /* log10(max(x,1e-10)), max(x, clip_max-8), (x+4)/4  (north_star)  */
+} yoho_norm;
+
+typedef enum yoho_compute {
+  YOHO_COMPUTE_FP32 = 0, /* fp32 operands and accumulation (SIMT), 1e-4 parity path      */
+  YOHO_COMPUTE_BF16 = 1  /* bf16 operands, fp32 accumulation on tcgen05 tensor cores     */
+} yoho_compute;
+
+/* ---- library / context ------------------------------------------------------------- */
+
+int yoho_abi_version(void);
+const char* yoho_last_error(void);
+
+/* Creates the per-device state (FFT twiddles, window, driver entry points).  May allocate
+ * and synchronise.  One context per device; safe to share between host threads. */
+int yoho_ctx_create(int device, yoho_ctx** out);
+int yoho_ctx_destroy(yoho_ctx* ctx);
+
+/* ---- frontend ---------------------------------------------------------------------- */
+
+/* Frames produced by jax.scipy.signal.stft(x, nperseg=n_fft, noverlap=n_fft-hop,
+ * boundary=None) with its default padded=True (audio.py:33): 480000 -> 2999.
+ * Returns a negative yoho_status for invalid arguments. */
+int yoho_stft_frames(int n_samples, int n_fft, int hop);
+
+/* Replaces mel_filter_banks(sr, n_fft, n_mels) as a *device constant*
+ * (mel_filterbanks.py:21-42, consumed at audio.py:35-36).  `host_filters` is the dense
+ * row-major (n_mels, n_bins) float32 matrix on the HOST; it is packed into per-row
+ * bands [lo, hi) covering every non-zero and uploaded.  Setup call: may allocate and
+ * synchronise. */
+int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, int n_mels, int n_bins,
+                           yoho_filterbank** out);
+int yoho_filterbank_destroy(yoho_filterbank* fb);
+
+size_t yoho_logmel_workspace_bytes(int batch, int n_samples, int n_fft, int hop, int n_mels);
+
+/* Replaces mel_spectogram(audio, n_fft, hop_len, sample_rate, n_mels) (audio.py:32-37;
+ * norm = YOHO_NORM_NONE) and, fused, normalize_spectogram (audio.py:53-58;
+ * YOHO_NORM_REFERENCE) or the Whisper normaliser (YOHO_NORM_WHISPER).
+ *   pcm  (batch, n_samples) float32      out  (batch, frames, n_mels) float32
+ * Kernels exist for n_fft = 400, hop = 160 (every configuration in the reference and in
+ * BASELINE.json); other values return YOHO_ERR_UNSUPPORTED. */
+int yoho_logmel_f32(yoho_ctx* ctx, const yoho_filterbank* fb, const float* pcm, int batch,
+                    int n_samples, int n_fft, int hop, float* out, int norm, void* ws,
+                    size_t ws_bytes, yoho_stream_t stream);
+
+/* Same with interleaved-free mono int16 PCM as ffmpeg delivers it (audio.py:11-18); samples
+ * are scaled by 1/32768 on load (whisper.py:249). */
+int yoho_logmel_s16(yoho_ctx* ctx, const yoho_filterbank* fb, const int16_t* pcm, int batch,
+                    int n_samples, int n_fft, int hop, float* out, int norm, void* ws,
+                    size_t ws_bytes, yoho_stream_t stream);
+
+size_t yoho_normalize_workspace_bytes(int batch, int frames, int n_mels);
+
+/* Stand-alone normalize_spectogram(spectogram) (audio.py:53-58) / Whisper normaliser on an
+ * existing (batch, frames, n_mels) float32 mel power spectrogram.  `out` may alias `spec`.
+ * norm must be YOHO_NORM_REFERENCE or YOHO_NORM_WHISPER. */
+int yoho_normalize_f32(yoho_ctx* ctx, const float* spec, int batch, int frames, int n_mels,
+                       float* out, int norm, void* ws, size_t ws_bytes, yoho_stream_t stream);
+
+/* ---- encoder ----------------------------------------------------------------------- */
+
+/* Shape of AudioEncoder(seq_len, dims, n_heads, n_layers) (whisper.py:117-122) plus the mel
+ * width of its input.  dims / n_heads must be 64 (true for every Whisper size). */
+typedef struct yoho_enc_desc {
+  int32_t n_mels;   /* input channels of Conv_0                    */
+  int32_t dims;     /* D                                            */
+  int32_t n_heads;  /* H                                            */
+  int32_t n_layers; /* L                                            */
+  int32_t seq_len;  /* rows of the sinusoid table (1500)            */
+} yoho_enc_desc;
+
+/* Number and order of the float32 tensors yoho_encoder_weights_pack consumes:
+ *   0 Conv_0.kernel (3, n_mels, D)   1 Conv_0.bias (D)
+ *   2 Conv_1.kernel (3, D, D)        3 Conv_1.bias (D)
+ *   4 sinusoid table (seq_len, D)    [SinPositionalEncoding has no params; built by the host
+ *                                     in the reference's float32 op order, whisper.py:11-17]
+ *   5 LayerNorm_0.scale (D)          6 LayerNorm_0.bias (D)            [final LN, whisper.py:134]
+ *   then for each EncoderBlock_i, 15 tensors (whisper.py:75-88, 31-35):
+ *     LayerNorm_0.scale, LayerNorm_0.bias,
+ *     query_proj.kernel (D,D), query_proj.bias, key_proj.kernel (D,D) [no bias],
+ *     value_proj.kernel (D,D), value_proj.bias, out_proj.kernel (D,D), out_proj.bias,
+ *     LayerNorm_1.scale, LayerNorm_1.bias,
+ *     Dense_0.kernel (D,4D), Dense_0.bias (4D), Dense_1.kernel (4D,D), Dense_1.bias (D)
+ * Kernels keep the Flax layout (in, out) / (k, in, out). */
+int yoho_encoder_num_tensors(const yoho_enc_desc* desc);
+
+size_t yoho_encoder_weights_bytes(const yoho_enc_desc* desc);
+
+/* Replaces "{'params': params}" of model.apply (whisper.py:258): copies the float32 tensors
+ * (host or device pointers) into `blob` and derives the packed bf16 operand copies
+ * ((out, in) K-major, q/k/v fused) on the device.  Asynchronous on `stream`; host source
+ * buffers must stay valid until the stream reaches this point. */
+int yoho_encoder_weights_pack(yoho_ctx* ctx, const yoho_enc_desc* desc, const float* const* tensors,
+                              int n_tensors, void* blob, size_t blob_bytes, yoho_stream_t stream);
+
+/* T = floor((frames + 2 - 3) / 2) + 1 (Conv_1: k=3, padding=1, strides=2; whisper.py:127). */
+int yoho_encoder_out_len(int frames);
+
+size_t yoho_encoder_workspace_bytes(const yoho_enc_desc* desc, int batch, int frames, int compute);
+
+/* Replaces model.apply({"params": params}, mel, method=Whisper.encode_audio)
+ * (whisper.py:194-195, 258) == AudioEncoder.__call__ (whisper.py:124-135).
+ *   mel (batch, frames, n_mels) float32  ->  out (batch, T, D) float32
+ * yoho_encoder_out_len(frames) must equal desc->seq_len (whisper.py:23 broadcasts). */
+int yoho_encoder_fwd(yoho_ctx* ctx, const yoho_enc_desc* desc, const void* blob, const float* mel,
+                     int batch, int frames, float* out, int compute, void* ws, size_t ws_bytes,
+                     yoho_stream_t stream);
+
+/* ---- test hooks (exercised by tests/, not part of the reference surface) ------------- */
+
+/* C (m, n) = A (m, k) @ W (k, n) + bias with the tcgen05 kernel: A, W float32 on the device,
+ * rounded to bf16 inside; used to unit-test the tensor-core path in isolation. epilogue:
+ * 0 bias, 1 bias+gelu(tanh). */
+size_t yoho_test_gemm_workspace_bytes(int m, int n, int k);
+int yoho_test_gemm_bf16(yoho_ctx* ctx, const float* a, const float* w, const float* bias, float* c,
+                        int m, int n, int k, int epilogue, void* ws, size_t ws_bytes,
+                        yoho_stream_t stream);
+
+/* softmax(q k^T / 8) v per (batch, head) with the tcgen05 attention kernel; qkv (batch, t, 3, h, 64)
+ * float32 (rounded to bf16 inside), out (batch, t, h*64) float32. */
+size_t yoho_test_attention_workspace_bytes(int batch, int t, int heads);
+int yoho_test_attention_bf16(yoho_ctx* ctx, const float* qkv, float* out, int batch, int t, int heads,
+                             void* ws, size_t ws_bytes, yoho_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YOHO_B200_H_ */

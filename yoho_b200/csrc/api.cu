@@ -1,0 +1,150 @@
+// Context, filterbank and error plumbing of the C ABI (include/yoho_b200.h).
+#include "common.cuh"
+
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+
+namespace yoho {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+}  // namespace yoho
+
+using namespace yoho;
+
+extern "C" int yoho_abi_version(void) { return YOHO_ABI_VERSION; }
+extern "C" const char* yoho_last_error(void) { return g_error; }
+
+extern "C" int yoho_ctx_create(int device, yoho_ctx** out) {
+  if (!out) return fail(YOHO_ERR_INVALID, "yoho_ctx_create: out is null");
+  *out = nullptr;
+  int count = 0;
+  YOHO_CUDA_CHECK(cudaGetDeviceCount(&count));
+  if (device < 0 || device >= count) return fail(YOHO_ERR_INVALID, "yoho_ctx_create: device %d of %d", device, count);
+  YOHO_CUDA_CHECK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  YOHO_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(YOHO_ERR_ARCH, "yoho_ctx_create: device %d (%s) is sm_%d%d; this library is built for sm_100a only and has no fallback",
+                device, prop.name, prop.major, prop.minor);
+  yoho_ctx* ctx = new (std::nothrow) yoho_ctx();
+  if (!ctx) return fail(YOHO_ERR_INVALID, "yoho_ctx_create: out of host memory");
+  ctx->device = device;
+  ctx->num_sms = prop.multiProcessorCount;
+  ctx->cc_major = prop.major;
+  ctx->cc_minor = prop.minor;
+
+  // Periodic Hann, scipy.signal.get_window('hann', 400): float64 then rounded to float32, exactly
+  // what jax.scipy.signal.stft multiplies by (reference audio.py:33).
+  const double kPi = 3.14159265358979323846;
+  std::vector<float> win(400);
+  double wsum = 0.0;
+  for (int n = 0; n < 400; ++n) {
+    win[n] = float(0.5 - 0.5 * std::cos(2.0 * kPi * n / 400.0));
+    wsum += double(win[n]);
+  }
+  ctx->window_sum = wsum;
+  std::vector<float2> tw(400);
+  for (int k1 = 0; k1 < 20; ++k1)
+    for (int n2 = 0; n2 < 20; ++n2) {
+      double ang = -2.0 * kPi * double(n2 * k1) / 400.0;
+      tw[k1 * 20 + n2] = make_float2(float(std::cos(ang)), float(std::sin(ang)));
+    }
+  cudaError_t e;
+  if ((e = cudaMalloc(&ctx->d_window, 400 * sizeof(float))) != cudaSuccess ||
+      (e = cudaMalloc(&ctx->d_twiddle, 400 * sizeof(float2))) != cudaSuccess ||
+      (e = cudaMemcpy(ctx->d_window, win.data(), 400 * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(ctx->d_twiddle, tw.data(), 400 * sizeof(float2), cudaMemcpyHostToDevice)) != cudaSuccess) {
+    yoho_ctx_destroy(ctx);
+    return fail(YOHO_ERR_CUDA, "yoho_ctx_create: %s", cudaGetErrorString(e));
+  }
+  // cuTensorMapEncodeTiled without linking libcuda.
+  cudaDriverEntryPointQueryResult qres;
+  void* fn = nullptr;
+  e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+    yoho_ctx_destroy(ctx);
+    return fail(YOHO_ERR_CUDA, "yoho_ctx_create: cuTensorMapEncodeTiled entry point unavailable");
+  }
+  ctx->encode_tiled = fn;
+  *out = ctx;
+  return YOHO_OK;
+}
+
+extern "C" int yoho_ctx_destroy(yoho_ctx* ctx) {
+  if (!ctx) return YOHO_OK;
+  if (ctx->d_window) cudaFree(ctx->d_window);
+  if (ctx->d_twiddle) cudaFree(ctx->d_twiddle);
+  delete ctx;
+  return YOHO_OK;
+}
+
+extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, int n_mels, int n_bins,
+                                      yoho_filterbank** out) {
+  if (!ctx || !host_filters || !out) return fail(YOHO_ERR_INVALID, "yoho_filterbank_create: null argument");
+  *out = nullptr;
+  if (n_mels <= 0 || n_bins <= 0) return fail(YOHO_ERR_INVALID, "yoho_filterbank_create: shape (%d, %d)", n_mels, n_bins);
+  YOHO_CUDA_CHECK(cudaSetDevice(ctx->device));
+  std::vector<int> lo(n_mels, 0), len(n_mels, 0);
+  int max_len = 1;
+  for (int m = 0; m < n_mels; ++m) {
+    int first = -1, last = -1;
+    for (int k = 0; k < n_bins; ++k)
+      if (host_filters[size_t(m) * n_bins + k] != 0.0f) { if (first < 0) first = k; last = k; }
+    if (first >= 0) { lo[m] = first; len[m] = last - first + 1; }
+    if (len[m] > max_len) max_len = len[m];
+  }
+  const int stride = (max_len + 3) / 4 * 4;
+  // |2 X[k]|^2 comes out of the packed-pair FFT; stft scales by 1/sum(w) (scaling='spectrum').
+  const double scale = 0.25 / (ctx->window_sum * ctx->window_sum);
+  std::vector<float> w(size_t(n_mels) * stride, 0.0f);
+  for (int m = 0; m < n_mels; ++m)
+    for (int j = 0; j < len[m]; ++j)
+      w[size_t(m) * stride + j] = float(double(host_filters[size_t(m) * n_bins + lo[m] + j]) * scale);
+  yoho_filterbank* fb = new (std::nothrow) yoho_filterbank();
+  if (!fb) return fail(YOHO_ERR_INVALID, "yoho_filterbank_create: out of host memory");
+  fb->device = ctx->device;
+  fb->n_mels = n_mels;
+  fb->n_bins = n_bins;
+  fb->band_stride = stride;
+  fb->power_scale = scale;
+  cudaError_t e;
+  if ((e = cudaMalloc(&fb->d_lo, n_mels * sizeof(int))) != cudaSuccess ||
+      (e = cudaMalloc(&fb->d_len, n_mels * sizeof(int))) != cudaSuccess ||
+      (e = cudaMalloc(&fb->d_weights, w.size() * sizeof(float))) != cudaSuccess ||
+      (e = cudaMemcpy(fb->d_lo, lo.data(), n_mels * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(fb->d_len, len.data(), n_mels * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(fb->d_weights, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess) {
+    yoho_filterbank_destroy(fb);
+    return fail(YOHO_ERR_CUDA, "yoho_filterbank_create: %s", cudaGetErrorString(e));
+  }
+  *out = fb;
+  return YOHO_OK;
+}
+
+extern "C" int yoho_filterbank_destroy(yoho_filterbank* fb) {
+  if (!fb) return YOHO_OK;
+  if (fb->d_lo) cudaFree(fb->d_lo);
+  if (fb->d_len) cudaFree(fb->d_len);
+  if (fb->d_weights) cudaFree(fb->d_weights);
+  delete fb;
+  return YOHO_OK;
+}

@@ -1,0 +1,166 @@
+// Memory-bound helpers of the encoder: LayerNorm, casts, weight packing, conv-stem im2col.
+#include "kernels.cuh"
+
+namespace yoho {
+
+constexpr int kLnMaxVec = 10;  // float4 per lane -> dims <= 1280
+
+__device__ __forceinline__ void store4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void store4(__nv_bfloat16* p, float4 v) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<uint32_t*>(&lo);
+  u.y = *reinterpret_cast<uint32_t*>(&hi);
+  *reinterpret_cast<uint2*>(p) = u;
+}
+
+// One warp per row.  Reference whisper.py:77,82,134 (flax nn.LayerNorm defaults).
+template <typename OutT>
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const float* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ bias,
+                 OutT* __restrict__ y, int rows, int dims) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int nvec = dims >> 2;
+  const float4* xr = reinterpret_cast<const float4*>(x + size_t(row) * dims);
+  float4 v[kLnMaxVec];
+  float s = 0.0f, q = 0.0f;
+#pragma unroll
+  for (int i = 0; i < kLnMaxVec; ++i) {
+    int idx = i * 32 + lane;
+    if (idx < nvec) {
+      v[i] = xr[idx];
+      s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+      q = fmaf(v[i].x, v[i].x, fmaf(v[i].y, v[i].y, fmaf(v[i].z, v[i].z, fmaf(v[i].w, v[i].w, q))));
+    }
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  const float mean = s / float(dims);
+  const float var = fmaxf(0.0f, q / float(dims) - mean * mean);
+  const float rstd = rsqrtf(var + 1e-6f);
+  const float4* sc = reinterpret_cast<const float4*>(scale);
+  const float4* bi = reinterpret_cast<const float4*>(bias);
+  OutT* yr = y + size_t(row) * dims;
+#pragma unroll
+  for (int i = 0; i < kLnMaxVec; ++i) {
+    int idx = i * 32 + lane;
+    if (idx < nvec) {
+      float4 g = __ldg(sc + idx), b = __ldg(bi + idx), o;
+      o.x = fmaf((v[i].x - mean) * rstd, g.x, b.x);
+      o.y = fmaf((v[i].y - mean) * rstd, g.y, b.y);
+      o.z = fmaf((v[i].z - mean) * rstd, g.z, b.z);
+      o.w = fmaf((v[i].w - mean) * rstd, g.w, b.w);
+      store4(yr + idx * 4, o);
+    }
+  }
+}
+
+template <typename OutT>
+static int launch_layernorm(const float* x, const float* scale, const float* bias, OutT* y, int rows, int dims, cudaStream_t s) {
+  if (dims % 4 != 0 || dims > kLnMaxVec * 128) return fail(YOHO_ERR_UNSUPPORTED, "layernorm: dims=%d (need multiple of 4, <= %d)", dims, kLnMaxVec * 128);
+  if (rows == 0) return YOHO_OK;
+  layernorm_kernel<OutT><<<ceil_div(rows, 8), 256, 0, s>>>(x, scale, bias, y, rows, dims);
+  YOHO_LAUNCH_CHECK("layernorm_kernel");
+  return YOHO_OK;
+}
+int launch_layernorm_f32(const float* x, const float* sc, const float* b, float* y, int rows, int dims, cudaStream_t s) {
+  return launch_layernorm<float>(x, sc, b, y, rows, dims, s);
+}
+int launch_layernorm_bf16(const float* x, const float* sc, const float* b, __nv_bfloat16* y, int rows, int dims, cudaStream_t s) {
+  return launch_layernorm<__nv_bfloat16>(x, sc, b, y, rows, dims, s);
+}
+
+// dst[n][k] = bf16(src[k][n]) through a 32x33 shared tile; columns k..ld_dst-1 are zeroed.
+__global__ void transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int k, int n, int ld_dst) {
+  __shared__ float tile[32][33];
+  const int k0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    int kk = k0 + j, nn = n0 + threadIdx.x;
+    tile[j][threadIdx.x] = (kk < k && nn < n) ? src[size_t(kk) * n + nn] : 0.0f;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+    int nn = n0 + j, kk = k0 + threadIdx.x;
+    if (nn < n && kk < ld_dst) dst[size_t(nn) * ld_dst + kk] = __float2bfloat16_rn(tile[threadIdx.x][j]);
+  }
+}
+int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, int ld_dst, cudaStream_t s) {
+  dim3 grid(ceil_div(n, 32), ceil_div(ld_dst, 32));
+  transpose_cast_kernel<<<grid, dim3(32, 8), 0, s>>>(src, dst, k, n, ld_dst);
+  YOHO_LAUNCH_CHECK("transpose_cast_kernel");
+  return YOHO_OK;
+}
+
+__global__ void cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n) {
+  size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const size_t step = size_t(gridDim.x) * blockDim.x;
+  for (; i < n; i += step) dst[i] = __float2bfloat16_rn(src[i]);
+}
+__global__ void cast_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, size_t n) {
+  size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const size_t step = size_t(gridDim.x) * blockDim.x;
+  for (; i < n; i += step) dst[i] = __bfloat162float(src[i]);
+}
+static int grid_for(size_t n) { size_t g = (n + 255) / 256; return int(g > 148 * 32 ? 148 * 32 : (g ? g : 1)); }
+int launch_cast_bf16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t s) {
+  cast_bf16_kernel<<<grid_for(n), 256, 0, s>>>(src, dst, n);
+  YOHO_LAUNCH_CHECK("cast_bf16_kernel");
+  return YOHO_OK;
+}
+int launch_cast_f32(const __nv_bfloat16* src, float* dst, size_t n, cudaStream_t s) {
+  cast_f32_kernel<<<grid_for(n), 256, 0, s>>>(src, dst, n);
+  YOHO_LAUNCH_CHECK("cast_f32_kernel");
+  return YOHO_OK;
+}
+
+// One CTA per (clip, group of rows): dst[b][t][tap*M + c] = mel[b][t+tap-1][c] (zero outside [0,F)),
+// columns 3M..k0-1 and rows F..Fp-1 zero.  Replaces the zero padding of nn.Conv(padding=1)
+// (whisper.py:125) so that Conv_0 becomes one plain K-major GEMM.
+__global__ void __launch_bounds__(256)
+mel_im2col_kernel(const float* __restrict__ mel, __nv_bfloat16* __restrict__ dst, int frames, int frames_padded, int n_mels, int k0) {
+  const int b = blockIdx.y;
+  const float* src = mel + size_t(b) * frames * n_mels;
+  __nv_bfloat16* out = dst + size_t(b) * frames_padded * k0;
+  const int rows_per_cta = 16;
+  const int t0 = blockIdx.x * rows_per_cta;
+  const int half = k0 >> 1;  // write bf16 pairs
+  for (int i = threadIdx.x; i < rows_per_cta * half; i += blockDim.x) {
+    int r = i / half, cp = i - r * half;
+    int t = t0 + r;
+    if (t >= frames_padded) break;
+    float v[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      int col = cp * 2 + e;
+      int tap = col / n_mels, c = col - tap * n_mels;
+      int ts = t + tap - 1;
+      v[e] = (t < frames && tap < 3 && ts >= 0 && ts < frames) ? __ldg(src + size_t(ts) * n_mels + c) : 0.0f;
+    }
+    __nv_bfloat162 p = __floats2bfloat162_rn(v[0], v[1]);
+    *reinterpret_cast<__nv_bfloat162*>(out + size_t(t) * k0 + cp * 2) = p;
+  }
+}
+int launch_mel_im2col(const float* mel, __nv_bfloat16* dst, int batch, int frames, int frames_padded, int n_mels, int k0, cudaStream_t s) {
+  if (k0 % 2 != 0 || k0 < 3 * n_mels) return fail(YOHO_ERR_INVALID, "mel_im2col: k0=%d", k0);
+  if (batch == 0) return YOHO_OK;
+  for (int b0 = 0; b0 < batch; b0 += 65535) {
+    int nb = batch - b0 < 65535 ? batch - b0 : 65535;
+    mel_im2col_kernel<<<dim3(ceil_div(frames_padded, 16), nb), 256, 0, s>>>(
+        mel + size_t(b0) * frames * n_mels, dst + size_t(b0) * frames_padded * k0, frames, frames_padded, n_mels, k0);
+    YOHO_LAUNCH_CHECK("mel_im2col_kernel");
+  }
+  return YOHO_OK;
+}
+
+int launch_fill_zero(void* p, size_t bytes, cudaStream_t s) {
+  cudaError_t e = cudaMemsetAsync(p, 0, bytes, s);
+  if (e != cudaSuccess) return fail(YOHO_ERR_CUDA, "cudaMemsetAsync: %s", cudaGetErrorString(e));
+  return YOHO_OK;
+}
+
+}  // namespace yoho

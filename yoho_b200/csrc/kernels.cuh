@@ -1,0 +1,64 @@
+// Internal launch interface between the encoder driver (encoder.cu) and the kernel files.
+#pragma once
+#include "common.cuh"
+
+namespace yoho {
+
+// ---------------------------------------------------------------- elementwise.cu
+// LayerNorm over the last axis (flax nn.LayerNorm: eps 1e-6, var = E[x^2]-E[x]^2 >= 0).
+int launch_layernorm_f32(const float* x, const float* scale, const float* bias, float* y, int rows, int dims, cudaStream_t s);
+int launch_layernorm_bf16(const float* x, const float* scale, const float* bias, __nv_bfloat16* y, int rows, int dims, cudaStream_t s);
+// dst (n, k) bf16 = transpose of src (k, n) float32; dst row stride ld_dst (>= k), tail zero-filled.
+int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, int ld_dst, cudaStream_t s);
+int launch_cast_bf16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t s);
+int launch_cast_f32(const __nv_bfloat16* src, float* dst, size_t n, cudaStream_t s);
+// mel (B, F, M) float32 -> (B, Fp, K0) bf16 rows [x[t-1], x[t], x[t+1], 0...]; rows t >= F are zero.
+int launch_mel_im2col(const float* mel, __nv_bfloat16* dst, int batch, int frames, int frames_padded, int n_mels, int k0, cudaStream_t s);
+int launch_fill_zero(void* p, size_t bytes, cudaStream_t s);
+
+// ---------------------------------------------------------------- encoder_fp32.cu (SIMT, 1e-4 path)
+struct SgemmArgs {
+  const float* a = nullptr; const float* b = nullptr; float* c = nullptr;
+  int m = 0, n = 0, k = 0;
+  int lda = 0, ldb = 0, ldc = 0;
+  int b_transposed = 0;            // 0: b is (k, n) row-major; 1: b is (n, k) row-major
+  // conv mode (a is (batch, conv_len, conv_ch)): row -> (clip, t), k -> (tap, ch), zero padding 1
+  int conv = 0, conv_len = 0, conv_out = 0, conv_ch = 0, conv_stride = 1;
+  // batching over blockIdx.z = z1 * nz2 + z2
+  int nz1 = 1, nz2 = 1;
+  long long sa1 = 0, sa2 = 0, sb1 = 0, sb2 = 0, sc1 = 0, sc2 = 0;
+  // epilogue: v = alpha*acc + bias[n]; gelu; + pos[(row % pos_period), n]; c (+)= v
+  float alpha = 1.0f;
+  const float* bias = nullptr;
+  int gelu = 0;
+  const float* pos = nullptr; int pos_period = 1;
+  int accumulate = 0;
+};
+int launch_sgemm(const SgemmArgs& a, cudaStream_t s);
+int launch_softmax_rows(float* x, long long rows, int cols, cudaStream_t s);
+
+// ---------------------------------------------------------------- gemm_sm100.cu (tcgen05)
+struct TapSpec { int col_off; int row_off; };
+struct GemmBf16Args {
+  // A: bf16, viewed as (batch, rows_per_batch, a_cols) row-major, row stride a_ld elements
+  const __nv_bfloat16* a = nullptr; int a_ld = 0; int a_cols = 0;
+  int batch = 1; int rows_per_batch = 0;
+  // W: bf16 (n, k_total) row-major ("K-major"), k_total = n_taps * k_per_tap (zero padded to 64)
+  const __nv_bfloat16* w = nullptr; int n = 0; int k_per_tap = 0; int n_taps = 1;
+  TapSpec taps[3] = {{0, 0}, {0, 0}, {0, 0}};
+  // output: row index = clip * rows_per_batch + r, row stride ldc elements
+  __nv_bfloat16* out_bf16 = nullptr; float* out_f32 = nullptr; int ldc = 0;
+  const float* bias = nullptr;     // (n) or null
+  int gelu = 0;
+  const float* pos = nullptr;      // (rows_per_batch.., n): + pos[r % pos_period][col]
+  int pos_period = 1;
+  int accumulate = 0;              // out_f32 += value (residual stream)
+  int mask_period = 0, mask_valid = 0;  // if mask_period: rows with (r % mask_period) >= mask_valid store 0
+};
+int launch_gemm_bf16(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s);
+
+// ---------------------------------------------------------------- attention_sm100.cu (tcgen05)
+// qkv (batch, t, 3*dims) bf16 with q | k | v column blocks, heads of 64; out (batch, t, dims) bf16.
+int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16* out, int batch, int t, int heads, cudaStream_t s);
+
+}  // namespace yoho

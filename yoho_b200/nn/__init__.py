@@ -1,0 +1,5 @@
+from .whisper import (AudioEncoder, Whisper, conv_out_len, flatten_encoder_params, init_encoder_params,
+                      sin_positional_encoding)
+
+__all__ = ["AudioEncoder", "Whisper", "conv_out_len", "flatten_encoder_params", "init_encoder_params",
+           "sin_positional_encoding"]
