@@ -157,6 +157,20 @@ int yoho_encoder_fwd(yoho_ctx* ctx, const yoho_enc_desc* desc, const void* blob,
                      int batch, int frames, float* out, int compute, void* ws, size_t ws_bytes,
                      yoho_stream_t stream);
 
+/* ---- measurement hooks (bench.py; not part of the reference surface) ------------------ */
+
+/* Kernels launched by this library in this process so far (the `gpu_launches` evidence). */
+long long yoho_launch_count(void);
+
+/* Optional per-kernel-class CUDA-event profiler: while enabled every launch group is bracketed by
+ * events on its own stream (no synchronisation); yoho_prof_collect synchronises on them and sums, per
+ * class, the device time in ms, the algorithmic work (FLOP for the tcgen05 classes, bytes for the
+ * memory-bound ones) and the number of groups.  yoho_prof_enable(0/1) clears previous records. */
+int yoho_prof_enable(int on);
+int yoho_prof_num_classes(void);
+const char* yoho_prof_class_name(int cls);
+int yoho_prof_collect(double* ms, double* work, long long* launches, int n);
+
 /* ---- test hooks (exercised by tests/, not part of the reference surface) ------------- */
 
 /* C (m, n) = A (m, k) @ W (k, n) + bias with the tcgen05 kernel: A, W float32 on the device,

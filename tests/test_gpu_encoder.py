@@ -1,0 +1,156 @@
+"""GPU parity tests of the Whisper audio encoder: product path (Flax-style apply -> ctypes -> C ABI ->
+sm_100a kernels) against the float64 oracle / golden vectors.
+Tolerances (BASELINE.json north_star): fp32 path 1e-4; bf16 path 2e-2 max-relative
+(max|ours - oracle| / max|oracle|)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+TOL_FP32 = 1e-4
+TOL_BF16 = 2e-2
+
+
+@pytest.fixture(scope="module")
+def rt(built_library):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from yoho_b200.runtime import get_runtime
+    return get_runtime()
+
+
+def _bf16(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a, np.float32)).to(torch.bfloat16).to(torch.float32).numpy()
+
+
+def _max_rel(got, want):
+    return float(np.abs(got - want).max() / np.abs(want).max())
+
+
+# ------------------------------------------------------------------ tcgen05 GEMM in isolation
+@pytest.mark.parametrize("m,n,k,epi", [(128, 128, 64, 0), (256, 256, 128, 0), (1000, 384, 192, 0), (300, 768, 768, 1),
+                                       (4099, 1152, 384, 0), (129, 160, 72, 1), (20000, 2304, 768, 0), (513, 512, 3072, 0)])
+def test_tcgen05_gemm(rt, m, n, k, epi):
+    import torch
+    rng = np.random.default_rng(m + n + k)
+    a = rng.standard_normal((m, k)).astype(np.float32)
+    w = (rng.standard_normal((k, n)) / np.sqrt(k)).astype(np.float32)
+    bias = rng.standard_normal(n).astype(np.float32)
+    want = _bf16(a).astype(np.float64) @ _bf16(w).astype(np.float64) + bias
+    if epi == 1:
+        want = 0.5 * want * (1 + np.tanh(np.sqrt(2 / np.pi) * (want + 0.044715 * want ** 3)))
+    ad, wd, bd = (torch.from_numpy(v).cuda() for v in (a, w, bias))
+    out = torch.full((m, n), float("nan"), device="cuda")
+    nbytes = rt.lib.yoho_test_gemm_workspace_bytes(m, n, k)
+    ws = rt.workspace("test", nbytes)
+    from yoho_b200._lib import check
+    check(rt.lib.yoho_test_gemm_bf16(rt.ctx, C.c_void_p(ad.data_ptr()), C.c_void_p(wd.data_ptr()), C.c_void_p(bd.data_ptr()),
+                                     C.c_void_p(out.data_ptr()), m, n, k, epi, C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= 2e-3 * max(1.0, np.abs(want).max())       # fp32 accumulate; tanh.approx in the GELU case
+
+
+# ------------------------------------------------------------------ tcgen05 attention in isolation
+@pytest.mark.parametrize("batch,t,heads", [(1, 128, 1), (2, 100, 2), (1, 1500, 2), (3, 300, 6), (2, 257, 1)])
+def test_tcgen05_attention(rt, batch, t, heads):
+    import torch
+    rng = np.random.default_rng(batch * 1000 + t + heads)
+    qkv = rng.standard_normal((batch, t, 3, heads, 64)).astype(np.float32)
+    qkv[:, :, 0] *= 2.0                                                  # sharper softmax
+    r = _bf16(qkv).astype(np.float64)
+    q, k, v = (r[:, :, i].transpose(0, 2, 1, 3) for i in range(3))       # (B, H, T, 64)
+    s = q @ k.transpose(0, 1, 3, 2) / 8.0
+    p = np.exp(s - s.max(-1, keepdims=True))
+    p /= p.sum(-1, keepdims=True)
+    want = (p @ v).transpose(0, 2, 1, 3).reshape(batch, t, heads * 64)
+    qd = torch.from_numpy(qkv).cuda()
+    out = torch.full((batch, t, heads * 64), float("nan"), device="cuda")
+    nbytes = rt.lib.yoho_test_attention_workspace_bytes(batch, t, heads)
+    ws = rt.workspace("test", nbytes)
+    from yoho_b200._lib import check
+    check(rt.lib.yoho_test_attention_bf16(rt.ctx, C.c_void_p(qd.data_ptr()), C.c_void_p(out.data_ptr()), batch, t, heads,
+                                          C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= 1.5e-2 * np.abs(want).max()       # P and the output are rounded to bf16
+
+
+# ------------------------------------------------------------------ whole encoder
+def _golden(golden_dir):
+    from yoho_b200.nn import AudioEncoder, init_encoder_params
+    g = np.load(golden_dir / "encoder_golden.npz")
+    params = init_encoder_params(int(g["n_mels"]), int(g["dims"]), int(g["n_layers"]), seed=int(g["seed"]))
+    model = AudioEncoder(seq_len=100, dims=int(g["dims"]), n_heads=int(g["n_heads"]), n_layers=int(g["n_layers"]))
+    return g, params, model
+
+
+def test_encoder_fp32_golden(rt, golden_dir):
+    g, params, model = _golden(golden_dir)
+    out = model.apply({"params": params}, g["mel"], compute="fp32")
+    assert isinstance(out, np.ndarray) and out.shape == (2, 100, 128) and out.dtype == np.float32
+    assert np.abs(out - g["out"]).max() <= TOL_FP32
+
+
+def test_encoder_bf16_golden(rt, golden_dir):
+    g, params, model = _golden(golden_dir)
+    out = model.apply({"params": params}, g["mel"], compute="bf16")
+    assert np.isfinite(out).all()
+    assert _max_rel(out, g["out"]) <= TOL_BF16
+
+
+@pytest.mark.parametrize("frames", [2999, 3000])
+def test_whisper_tiny_full_clip(rt, frames):
+    """BASELINE.json configs[0]: Whisper-tiny, batch 1, one 30 s clip, through Whisper.apply(method=encode_audio)."""
+    from oracle import encoder as eo
+    from oracle import frontend as fe
+    from yoho_b200.nn import Whisper, init_encoder_params
+    from yoho_b200.synth import synth_clip
+    n_mels, dims, heads, layers = 80, 384, 6, 4
+    n_samples = 480000 if frames == 2999 else 480240
+    mel = fe.log_mel(synth_clip(0, n_samples)[None], norm_mode=1).astype(np.float32)
+    assert mel.shape == (1, frames, n_mels)
+    params = init_encoder_params(n_mels, dims, layers, seed=42)
+    want = eo.audio_encoder(params, mel, heads, np.float64)
+    model = Whisper(audio_dims=dims, audio_seq_len=1500, audio_heads=heads, audio_layers=layers)
+    variables = {"params": {"audio_encoder": params}}
+    out32 = model.apply(variables, mel, method=Whisper.encode_audio, compute="fp32")
+    assert out32.shape == (1, 1500, dims)
+    assert np.abs(out32 - want).max() <= TOL_FP32
+    out16 = model.apply(variables, mel, method=Whisper.encode_audio, compute="bf16")
+    assert _max_rel(out16, want) <= TOL_BF16
+
+
+def test_pipeline_pcm_to_states_batch(rt):
+    """log-mel kernels feeding the encoder on the device, batch of 4 base-size clips; bf16 vs fp32 path, and
+    batch independence (a property that holds at any size)."""
+    import torch
+    from yoho_b200.nn import AudioEncoder, init_encoder_params
+    from yoho_b200.preprocessing import log_mel_spectogram
+    from yoho_b200.synth import synth_batch
+    n_mels, dims, heads, layers = 80, 512, 8, 6
+    pcm = torch.from_numpy(synth_batch(4, 480000)).cuda()
+    mel = log_mel_spectogram(pcm, norm="reference")
+    params = init_encoder_params(n_mels, dims, layers, seed=3)
+    model = AudioEncoder(1500, dims, heads, layers)
+    ref = model.apply({"params": params}, mel, compute="fp32")
+    out = model.apply({"params": params}, mel, compute="bf16")
+    assert out.is_cuda and out.shape == (4, 1500, dims)
+    assert float((out - ref).abs().max() / ref.abs().max()) <= TOL_BF16
+    alone = model.apply({"params": params}, mel[2:3].contiguous(), compute="bf16")
+    assert torch.equal(alone[0], out[2])
+
+
+def test_shape_mismatch_errors(rt):
+    from yoho_b200.nn import AudioEncoder, init_encoder_params
+    params = init_encoder_params(80, 128, 1, seed=0)
+    with pytest.raises(ValueError, match="positions"):
+        AudioEncoder(1500, 128, 2, 1).apply({"params": params}, np.zeros((1, 199, 80), np.float32))
+    with pytest.raises(ValueError, match="Conv_0"):
+        AudioEncoder(100, 128, 2, 1).apply({"params": params}, np.zeros((1, 199, 128), np.float32))

@@ -1,0 +1,187 @@
+"""Stage-by-stage numerical diagnostics on the GPU box (prints error metrics, not just pass/fail).
+
+    python tools/gpu_debug.py <stage> [...]     stages: frontend fp32 gemm attention bf16 perf
+
+Each stage is meant to run in its own process under `timeout` (see tools/gpu_debug.sh) so that a hung
+kernel cannot take the whole gpurun call with it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+
+from oracle import encoder as eo  # noqa: E402
+from oracle import frontend as fe  # noqa: E402
+from yoho_b200._lib import check  # noqa: E402
+from yoho_b200.runtime import get_runtime  # noqa: E402
+from yoho_b200.synth import synth_batch  # noqa: E402
+
+GOLD = ROOT / "tests" / "golden"
+
+
+def bf16(a):
+    return torch.from_numpy(np.ascontiguousarray(a, np.float32)).to(torch.bfloat16).to(torch.float32).numpy()
+
+
+def timed(fn, iters=5, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / iters
+
+
+def stage_frontend():
+    from yoho_b200 import preprocessing as pp
+    g = np.load(GOLD / "frontend_golden.npz")
+    x = g["audio"]
+    for m in (80, 128):
+        p = pp.mel_spectogram(x, 400, 160, 16000, m)
+        w = g[f"m{m}_power"]
+        rel = np.abs(p[:2] - w[:2]) / np.maximum(np.abs(w[:2]), 1e-30)
+        print(f"[frontend] M={m} power: max rel err {rel.max():.3e}  zero-clip max {np.abs(p[2]).max():.3e}")
+        for norm in ("reference", "whisper"):
+            o = pp.log_mel_spectogram(x, n_mels=m, norm=norm)
+            e = np.abs(o - g[f"m{m}_{norm}"])
+            print(f"[frontend] M={m} {norm}: max abs err clips0-2 {e[:3].max():.3e}  tonal clip {e[3].max():.3e}")
+    xb = synth_batch(3, 480000)
+    want = fe.log_mel(xb, norm_mode=1)
+    got = pp.log_mel_spectogram(xb, norm="reference")
+    print(f"[frontend] full 30 s x3 reference-norm max abs err {np.abs(got - want).max():.3e}")
+
+
+def stage_fp32():
+    from yoho_b200.nn import AudioEncoder, init_encoder_params
+    g = np.load(GOLD / "encoder_golden.npz")
+    params = init_encoder_params(80, 128, 2, seed=7)
+    out = AudioEncoder(100, 128, 2, 2).apply({"params": params}, g["mel"], compute="fp32")
+    print(f"[fp32] golden encoder max abs err {np.abs(out - g['out']).max():.3e} (max|y| {np.abs(g['out']).max():.2f})")
+
+
+def run_gemm(rt, a, w, bias, epi):
+    m, k = a.shape
+    n = w.shape[1]
+    ad, wd, bd = (torch.from_numpy(v).cuda() for v in (a, w, bias))
+    out = torch.full((m, n), float("nan"), device="cuda")
+    nbytes = rt.lib.yoho_test_gemm_workspace_bytes(m, n, k)
+    ws = rt.workspace("test", nbytes)
+    check(rt.lib.yoho_test_gemm_bf16(rt.ctx, C.c_void_p(ad.data_ptr()), C.c_void_p(wd.data_ptr()), C.c_void_p(bd.data_ptr()),
+                                     C.c_void_p(out.data_ptr()), m, n, k, epi, C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def stage_gemm():
+    rt = get_runtime()
+    for (m, n, k) in [(128, 128, 64), (128, 256, 64), (128, 128, 128), (256, 256, 256), (1000, 384, 192), (4099, 1152, 384), (129, 160, 72)]:
+        rng = np.random.default_rng(m + n + k)
+        a = rng.standard_normal((m, k)).astype(np.float32)
+        w = (rng.standard_normal((k, n)) / np.sqrt(k)).astype(np.float32)
+        bias = rng.standard_normal(n).astype(np.float32)
+        want = bf16(a).astype(np.float64) @ bf16(w).astype(np.float64) + bias
+        got = run_gemm(rt, a, w, bias, 0)
+        err = np.abs(got - want)
+        bad = ~np.isfinite(got)
+        print(f"[gemm] {m}x{n}x{k}: max err {np.nanmax(err):.3e} nan {int(bad.sum())} (max|c| {np.abs(want).max():.2f})")
+        if np.nanmax(err) > 1e-2 or bad.any():
+            # structure of the error: per 32-row x 32-col block
+            e = np.where(bad, 1e9, err)[: min(m, 128), : min(n, 256)]
+            blk = e[: e.shape[0] // 32 * 32, : e.shape[1] // 32 * 32].reshape(e.shape[0] // 32, 32, e.shape[1] // 32, 32).max(axis=(1, 3))
+            print("[gemm]   block max err (32x32 blocks of the first tile):\n", np.array2string(blk, precision=2, max_line_width=200))
+            print("[gemm]   got[0,:8]", got[0, :8], "\n[gemm]   want[0,:8]", want[0, :8])
+            # does it match a k-truncated product? (descriptor advance bugs)
+            for kk in (16, 32, 48, 64):
+                if kk <= k:
+                    part = bf16(a[:, :kk]).astype(np.float64) @ bf16(w[:kk]).astype(np.float64) + bias
+                    print(f"[gemm]   err vs first-{kk}-k partial: {np.nanmax(np.abs(got - part)):.3e}")
+
+
+def stage_attention():
+    rt = get_runtime()
+    for (batch, t, heads) in [(1, 128, 1), (1, 256, 1), (2, 100, 2), (1, 1500, 2)]:
+        rng = np.random.default_rng(t + heads)
+        qkv = rng.standard_normal((batch, t, 3, heads, 64)).astype(np.float32)
+        r = bf16(qkv).astype(np.float64)
+        q, k, v = (r[:, :, i].transpose(0, 2, 1, 3) for i in range(3))
+        s = q @ k.transpose(0, 1, 3, 2) / 8.0
+        p = np.exp(s - s.max(-1, keepdims=True))
+        p /= p.sum(-1, keepdims=True)
+        want = (p @ v).transpose(0, 2, 1, 3).reshape(batch, t, heads * 64)
+        qd = torch.from_numpy(qkv).cuda()
+        out = torch.full((batch, t, heads * 64), float("nan"), device="cuda")
+        nbytes = rt.lib.yoho_test_attention_workspace_bytes(batch, t, heads)
+        ws = rt.workspace("test", nbytes)
+        check(rt.lib.yoho_test_attention_bf16(rt.ctx, C.c_void_p(qd.data_ptr()), C.c_void_p(out.data_ptr()), batch, t, heads,
+                                              C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
+        torch.cuda.synchronize()
+        got = out.cpu().numpy()
+        err = np.abs(got - want)
+        print(f"[attention] B{batch} T{t} H{heads}: max err {np.nanmax(err):.3e} nan {int((~np.isfinite(got)).sum())} (max|o| {np.abs(want).max():.2f})")
+        if np.nanmax(err) > 3e-2:
+            vmean = v.mean(axis=2)  # uniform softmax would give this
+            print("[attention]   err vs uniform-softmax:", np.abs(got[0, :, :64] - vmean[0, 0]).max())
+            print("[attention]   got[0,0,:6]", got[0, 0, :6], " want", want[0, 0, :6])
+            rows = err[0].max(axis=1)
+            print("[attention]   per-row err (first 8, last 8):", rows[:8], rows[-8:])
+
+
+def stage_bf16():
+    from yoho_b200.nn import AudioEncoder, init_encoder_params
+    g = np.load(GOLD / "encoder_golden.npz")
+    params = init_encoder_params(80, 128, 2, seed=7)
+    model = AudioEncoder(100, 128, 2, 2)
+    out = model.apply({"params": params}, g["mel"], compute="bf16")
+    rel = np.abs(out - g["out"]).max() / np.abs(g["out"]).max()
+    print(f"[bf16] golden encoder max-rel err {rel:.3e} nan {int((~np.isfinite(out)).sum())}")
+    n_mels, dims, heads, layers = 80, 384, 6, 4
+    from yoho_b200.synth import synth_clip
+    mel = fe.log_mel(synth_clip(0)[None], norm_mode=1).astype(np.float32)
+    params = init_encoder_params(n_mels, dims, layers, seed=42)
+    want = eo.audio_encoder(params, mel, heads, np.float64)
+    model = AudioEncoder(1500, dims, heads, layers)
+    o32 = model.apply({"params": params}, mel, compute="fp32")
+    o16 = model.apply({"params": params}, mel, compute="bf16")
+    print(f"[bf16] tiny full clip: fp32 max abs err {np.abs(o32 - want).max():.3e}; bf16 max-rel {np.abs(o16 - want).max() / np.abs(want).max():.3e}")
+
+
+def stage_perf():
+    from yoho_b200 import preprocessing as pp
+    from yoho_b200.nn import AudioEncoder, init_encoder_params
+    B = 256
+    pcm = torch.from_numpy(synth_batch(B, 480000, unique=8)).cuda()
+    out = torch.empty((B, 2999, 80), device="cuda")
+    for norm in ("none", "reference"):
+        ms = timed(lambda: pp.log_mel_spectogram(pcm, norm=norm, out=out))
+        gbs = B * 2879680 / ms / 1e6
+        print(f"[perf] frontend B={B} norm={norm}: {ms:.3f} ms  {gbs:.0f} GB/s algorithmic ({gbs / 6540.2 * 100:.1f}% of measured HBM peak)")
+    mel = pp.log_mel_spectogram(pcm, norm="reference")
+    for name, (n_mels, dims, heads, layers), b in (("base", (80, 512, 8, 6), 64), ("small", (80, 768, 12, 12), 64)):
+        params = init_encoder_params(n_mels, dims, layers, seed=1)
+        model = AudioEncoder(1500, dims, heads, layers)
+        x = mel[:b].contiguous()
+        o = torch.empty((b, 1500, dims), device="cuda")
+        ms = timed(lambda: model.apply({"params": params}, x, compute="bf16", out=o), iters=3, warm=1)
+        gf = {"base": 87.37, "small": 344.16}[name]
+        print(f"[perf] encoder {name} B={b} bf16: {ms:.2f} ms  {b * gf / ms:.1f} TFLOP/s  {b * 30 / ms * 1000:.0f}x realtime")
+
+
+if __name__ == "__main__":
+    torch.cuda.init()
+    print("device:", torch.cuda.get_device_name(0))
+    for st in sys.argv[1:]:
+        t0 = time.time()
+        globals()[f"stage_{st}"]()
+        print(f"[{st}] done in {time.time() - t0:.1f}s", flush=True)

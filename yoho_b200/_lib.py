@@ -45,6 +45,11 @@ SIGNATURES = {
     "yoho_encoder_out_len": (_i, [_i]),
     "yoho_encoder_workspace_bytes": (_sz, [C.POINTER(EncDesc), _i, _i, _i]),
     "yoho_encoder_fwd": (_i, [_p, C.POINTER(EncDesc), _p, _p, _i, _i, _p, _i, _p, _sz, _p]),
+    "yoho_launch_count": (C.c_longlong, []),
+    "yoho_prof_enable": (_i, [_i]),
+    "yoho_prof_num_classes": (_i, []),
+    "yoho_prof_class_name": (C.c_char_p, [_i]),
+    "yoho_prof_collect": (_i, [C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_longlong), _i]),
     "yoho_test_gemm_workspace_bytes": (_sz, [_i, _i, _i]),
     "yoho_test_gemm_bf16": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _sz, _p]),
     "yoho_test_attention_workspace_bytes": (_sz, [_i, _i, _i]),

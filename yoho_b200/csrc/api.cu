@@ -1,7 +1,9 @@
 // Context, filterbank and error plumbing of the C ABI (include/yoho_b200.h).
 #include "common.cuh"
 
+#include <atomic>
 #include <cmath>
+#include <mutex>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -26,9 +28,74 @@ int fail(int code, const char* fmt, ...) {
   return code;
 }
 
+// ---- launch counter + event profiler ---------------------------------------------------------
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+struct ProfRecord { int cls; double work; cudaEvent_t start, stop; };
+static std::mutex g_prof_mutex;
+static bool g_prof_on = false;
+static std::vector<ProfRecord> g_prof_records;
+static std::vector<cudaEvent_t> g_event_pool;
+
+static cudaEvent_t pool_event() {
+  if (!g_event_pool.empty()) { cudaEvent_t e = g_event_pool.back(); g_event_pool.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+
+ProfScope::ProfScope(cudaStream_t s, int cls, double work) : stream(s), slot(-1) {
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
+  if (!g_prof_on) return;
+  ProfRecord r{cls, work, pool_event(), pool_event()};
+  if (!r.start || !r.stop) return;
+  cudaEventRecord(r.start, s);
+  g_prof_records.push_back(r);
+  slot = int(g_prof_records.size()) - 1;
+}
+ProfScope::~ProfScope() {
+  if (slot < 0) return;
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
+  if (slot < int(g_prof_records.size())) cudaEventRecord(g_prof_records[slot].stop, stream);
+}
+
 }  // namespace yoho
 
 using namespace yoho;
+
+extern "C" long long yoho_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+extern "C" int yoho_prof_enable(int on) {
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
+  for (auto& r : g_prof_records) { g_event_pool.push_back(r.start); g_event_pool.push_back(r.stop); }
+  g_prof_records.clear();
+  g_prof_on = on != 0;
+  return YOHO_OK;
+}
+
+extern "C" int yoho_prof_num_classes(void) { return kProfNumClasses; }
+
+extern "C" const char* yoho_prof_class_name(int cls) {
+  static const char* names[kProfNumClasses] = {"logmel", "normalize", "gemm_tcgen05", "attention_tcgen05", "layernorm", "other"};
+  return (cls >= 0 && cls < kProfNumClasses) ? names[cls] : "";
+}
+
+extern "C" int yoho_prof_collect(double* ms, double* work, long long* launches, int n) {
+  if (!ms || !work || !launches || n < kProfNumClasses) return fail(YOHO_ERR_INVALID, "yoho_prof_collect: need %d slots", kProfNumClasses);
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
+  for (int i = 0; i < n; ++i) { ms[i] = 0.0; work[i] = 0.0; launches[i] = 0; }
+  for (auto& r : g_prof_records) {
+    cudaError_t e = cudaEventSynchronize(r.stop);
+    if (e != cudaSuccess) return fail(YOHO_ERR_CUDA, "yoho_prof_collect: %s", cudaGetErrorString(e));
+    float t = 0.0f;
+    e = cudaEventElapsedTime(&t, r.start, r.stop);
+    if (e != cudaSuccess) return fail(YOHO_ERR_CUDA, "yoho_prof_collect: %s", cudaGetErrorString(e));
+    ms[r.cls] += t; work[r.cls] += r.work; launches[r.cls] += 1;
+  }
+  return YOHO_OK;
+}
 
 extern "C" int yoho_abi_version(void) { return YOHO_ABI_VERSION; }
 extern "C" const char* yoho_last_error(void) { return g_error; }

@@ -259,6 +259,7 @@ int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16
   if (r) return fail(YOHO_ERR_CUDA, "attention: cuTensorMapEncodeTiled failed with CUresult %d", r);
   YOHO_CUDA_CHECK(cudaFuncSetAttribute(attention_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(AttSmem))));
   dim3 grid(ceil_div(t, kTileQ), heads, batch);
+  ProfScope prof(s, kProfAttention, 4.0 * double(batch) * double(t) * double(t) * double(dims));
   attention_bf16_kernel<<<grid, kAttThreads, sizeof(AttSmem), s>>>(map, out, t, dims);
   YOHO_LAUNCH_CHECK("attention_bf16_kernel");
   return YOHO_OK;

@@ -24,11 +24,22 @@ int fail(int code, const char* fmt, ...);
 
 #define YOHO_LAUNCH_CHECK(name)                                                            \
   do {                                                                                     \
+    ::yoho::count_launch();                                                                \
     cudaError_t _e = cudaGetLastError();                                                   \
     if (_e != cudaSuccess)                                                                 \
       return ::yoho::fail(YOHO_ERR_CUDA, "launch of %s failed: %s", name,                  \
                           cudaGetErrorString(_e));                                         \
   } while (0)
+
+// ---- launch accounting and the optional per-kernel-class event profiler (bench.py roofline) ----
+enum ProfClass { kProfFrontend = 0, kProfNormalize, kProfGemm, kProfAttention, kProfLayerNorm, kProfOther, kProfNumClasses };
+void count_launch();
+// RAII: when profiling is enabled, brackets the launches issued in its lifetime with CUDA events on `s`.
+struct ProfScope {
+  ProfScope(cudaStream_t s, int cls, double work);
+  ~ProfScope();
+  cudaStream_t stream; int slot;
+};
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

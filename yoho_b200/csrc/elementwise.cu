@@ -64,6 +64,7 @@ template <typename OutT>
 static int launch_layernorm(const float* x, const float* scale, const float* bias, OutT* y, int rows, int dims, cudaStream_t s) {
   if (dims % 4 != 0 || dims > kLnMaxVec * 128) return fail(YOHO_ERR_UNSUPPORTED, "layernorm: dims=%d (need multiple of 4, <= %d)", dims, kLnMaxVec * 128);
   if (rows == 0) return YOHO_OK;
+  ProfScope prof(s, kProfLayerNorm, double(rows) * double(dims) * double(sizeof(float) + sizeof(OutT)));
   layernorm_kernel<OutT><<<ceil_div(rows, 8), 256, 0, s>>>(x, scale, bias, y, rows, dims);
   YOHO_LAUNCH_CHECK("layernorm_kernel");
   return YOHO_OK;
@@ -91,6 +92,7 @@ __global__ void transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat
 }
 int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, int ld_dst, cudaStream_t s) {
   dim3 grid(ceil_div(n, 32), ceil_div(ld_dst, 32));
+  ProfScope prof(s, kProfOther, double(k) * n * 6.0);
   transpose_cast_kernel<<<grid, dim3(32, 8), 0, s>>>(src, dst, k, n, ld_dst);
   YOHO_LAUNCH_CHECK("transpose_cast_kernel");
   return YOHO_OK;
@@ -108,11 +110,13 @@ __global__ void cast_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __
 }
 static int grid_for(size_t n) { size_t g = (n + 255) / 256; return int(g > 148 * 32 ? 148 * 32 : (g ? g : 1)); }
 int launch_cast_bf16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t s) {
+  ProfScope prof(s, kProfOther, double(n) * 6.0);
   cast_bf16_kernel<<<grid_for(n), 256, 0, s>>>(src, dst, n);
   YOHO_LAUNCH_CHECK("cast_bf16_kernel");
   return YOHO_OK;
 }
 int launch_cast_f32(const __nv_bfloat16* src, float* dst, size_t n, cudaStream_t s) {
+  ProfScope prof(s, kProfOther, double(n) * 6.0);
   cast_f32_kernel<<<grid_for(n), 256, 0, s>>>(src, dst, n);
   YOHO_LAUNCH_CHECK("cast_f32_kernel");
   return YOHO_OK;
@@ -148,6 +152,7 @@ mel_im2col_kernel(const float* __restrict__ mel, __nv_bfloat16* __restrict__ dst
 int launch_mel_im2col(const float* mel, __nv_bfloat16* dst, int batch, int frames, int frames_padded, int n_mels, int k0, cudaStream_t s) {
   if (k0 % 2 != 0 || k0 < 3 * n_mels) return fail(YOHO_ERR_INVALID, "mel_im2col: k0=%d", k0);
   if (batch == 0) return YOHO_OK;
+  ProfScope prof(s, kProfOther, double(batch) * (double(frames) * n_mels * 4.0 + double(frames_padded) * k0 * 2.0));
   for (int b0 = 0; b0 < batch; b0 += 65535) {
     int nb = batch - b0 < 65535 ? batch - b0 : 65535;
     mel_im2col_kernel<<<dim3(ceil_div(frames_padded, 16), nb), 256, 0, s>>>(

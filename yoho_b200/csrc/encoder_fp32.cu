@@ -150,6 +150,7 @@ int launch_sgemm(const SgemmArgs& a, cudaStream_t s) {
   if (nz > 65535) return fail(YOHO_ERR_UNSUPPORTED, "sgemm: %lld batches", nz);
   dim3 grid(ceil_div(a.n, BN), ceil_div(a.m, BM), unsigned(nz));
   if (grid.y > 65535) return fail(YOHO_ERR_UNSUPPORTED, "sgemm: m=%d too large for one launch", a.m);
+  ProfScope prof(s, kProfOther, 2.0 * double(nz) * a.m * double(a.n) * a.k);
   sgemm_kernel<<<grid, kSgemmThreads, 0, s>>>(a);
   YOHO_LAUNCH_CHECK("sgemm_kernel");
   return YOHO_OK;

@@ -394,11 +394,15 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
   const int chunk = (norm == YOHO_NORM_NONE) ? 65535 : clips_per_chunk(frames, fb->n_mels);
   for (int c0 = 0; c0 < batch; c0 += chunk) {
     int nb = batch - c0 < chunk ? batch - c0 : chunk;
-    logmel_kernel<T><<<dim3(tiles, nb), kThreads, sizeof(FrontendSmem), stream>>>(
-        pcm, n_samples, frames, c0, ctx->d_window, ctx->d_twiddle, fb->d_lo, fb->d_len, fb->d_weights,
-        fb->band_stride, fb->n_mels, out, stats, tiles, norm, vec_ok);
-    YOHO_LAUNCH_CHECK("logmel_kernel");
+    {
+      ProfScope prof(stream, kProfFrontend, double(nb) * (double(n_samples) * sizeof(T) + double(elems) * sizeof(float)));
+      logmel_kernel<T><<<dim3(tiles, nb), kThreads, sizeof(FrontendSmem), stream>>>(
+          pcm, n_samples, frames, c0, ctx->d_window, ctx->d_twiddle, fb->d_lo, fb->d_len, fb->d_weights,
+          fb->band_stride, fb->n_mels, out, stats, tiles, norm, vec_ok);
+      YOHO_LAUNCH_CHECK("logmel_kernel");
+    }
     if (norm != YOHO_NORM_NONE) {
+      ProfScope prof(stream, kProfNormalize, double(nb) * double(elems) * 2.0 * sizeof(float));
       normalize_apply_kernel<<<dim3(ceil_div(elems, kFinElemsPerCta), nb), kFinThreads, 0, stream>>>(
           out, out, elems, stats, tiles, c0, norm, 0);
       YOHO_LAUNCH_CHECK("normalize_apply_kernel");
@@ -460,6 +464,7 @@ extern "C" int yoho_normalize_f32(yoho_ctx* ctx, const float* spec, int batch, i
   float2* stats = static_cast<float2*>(ws);
   for (int c0 = 0; c0 < batch; c0 += 65535) {
     int nb = batch - c0 < 65535 ? batch - c0 : 65535;
+    ProfScope prof(stream, kProfNormalize, double(nb) * double(elems) * 3.0 * sizeof(float));
     spec_stats_kernel<<<dim3(tiles, nb), kStatThreads, 0, stream>>>(spec + size_t(c0) * elems, elems,
                                                                    stats + size_t(c0) * tiles, tiles, norm);
     YOHO_LAUNCH_CHECK("spec_stats_kernel");

@@ -257,6 +257,7 @@ static int launch_gemm_bn(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s) 
 
   YOHO_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   const int grid = p.total_tiles < ctx->num_sms ? p.total_tiles : ctx->num_sms;
+  ProfScope prof(s, kProfGemm, 2.0 * double(a.batch) * double(a.rows_per_batch) * double(a.n) * double(a.n_taps) * double(a.k_per_tap));
   gemm_bf16_kernel<BN><<<grid, kGemmThreads, Cfg::kSmemBytes, s>>>(map_a, map_w, p);
   YOHO_LAUNCH_CHECK("gemm_bf16_kernel");
   return YOHO_OK;
