@@ -1,0 +1,166 @@
+"""End-to-end clip pipeline: PCM -> log-mel -> Whisper audio encoder, the composition the reference
+runs at transcription_pretrain_no_voiceprints.py:172-179 + :198-203 and whisper.py:255-258
+(``mel_spectogram`` -> ``normalize_spectogram`` -> ``model.apply(..., method=Whisper.encode_audio)``).
+
+``ClipEncoder.encode`` keeps everything in HBM (device tensors in, device tensor out).
+``ClipEncoder.encode_host`` is the host-facing call: pinned host PCM in, pinned host encoder states
+out, with the H2D copy of chunk i+1 and the D2H copy of chunk i-1 overlapped with the kernels of
+chunk i on three CUDA streams (double-buffered device staging).  All arithmetic is libyoho_b200.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import MODEL_SHAPES
+from ._lib import COMPUTE_BF16, COMPUTE_FP32, NORM_NONE, NORM_REFERENCE, NORM_WHISPER, EncDesc, check
+from .nn.whisper import conv_out_len, flatten_encoder_params, sin_positional_encoding
+from .preprocessing.mel_filterbanks import mel_filter_banks
+from .runtime import get_runtime
+
+_NORM = {"none": NORM_NONE, "reference": NORM_REFERENCE, "whisper": NORM_WHISPER}
+_COMPUTE = {"bf16": COMPUTE_BF16, "fp32": COMPUTE_FP32}
+
+
+class ClipEncoder:
+    """Log-mel + encoder over batches of fixed-length clips on one GPU.
+
+    model: a name in ``MODEL_SHAPES`` or ``(n_mels, dims, n_heads, n_layers)``; params: the
+    reference's AudioEncoder parameter pytree (or ``{"params": {"audio_encoder": ...}}``).
+    """
+
+    def __init__(self, model, params: dict, n_samples: int = 480000, norm: str = "reference", compute: str = "bf16",
+                 sample_rate: int = 16000, n_fft: int = 400, hop: int = 160, device: int | None = None):
+        shape = MODEL_SHAPES[model] if isinstance(model, str) else tuple(model)
+        self.n_mels, self.dims, self.n_heads, self.n_layers = shape
+        self.rt = get_runtime(device)
+        lib = self.rt.lib
+        self.n_samples, self.n_fft, self.hop = int(n_samples), n_fft, hop
+        self.frames = check(lib.yoho_stft_frames(self.n_samples, n_fft, hop))
+        self.seq_len = conv_out_len(self.frames)
+        self.norm, self.compute = _NORM[norm], _COMPUTE[compute]
+        self.fb = self.rt.filterbank(mel_filter_banks(sample_rate, n_fft, self.n_mels))
+        params = params.get("params", params)
+        params = params.get("audio_encoder", params)
+        self.desc = EncDesc(self.n_mels, self.dims, self.n_heads, self.n_layers, self.seq_len)
+        tensors = flatten_encoder_params(params, self.n_layers, sin_positional_encoding(self.seq_len, self.dims))
+        self.blob = self.rt.packed_weights(params, self.desc, tensors)
+        self._mel: dict[int, torch.Tensor] = {}
+        self._stage: dict = {}
+        self._streams = None
+
+    # ---- device-resident path -------------------------------------------------------------
+    def _mel_buf(self, batch: int, slot: int = 0) -> torch.Tensor:
+        buf = self._mel.get(slot)
+        if buf is None or buf.shape[0] < batch:
+            buf = torch.empty((batch, self.frames, self.n_mels), dtype=torch.float32, device=self.rt.device)
+            self._mel[slot] = buf
+        return buf[:batch]
+
+    def logmel(self, pcm: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        """(B, n_samples) float32/int16 CUDA tensor -> (B, frames, n_mels) float32, on the current stream."""
+        rt, lib = self.rt, self.rt.lib
+        B = pcm.shape[0]
+        if pcm.shape[1] != self.n_samples or not pcm.is_cuda or not pcm.is_contiguous():
+            raise ValueError(f"pcm must be a contiguous CUDA tensor (B, {self.n_samples}); got {tuple(pcm.shape)} on {pcm.device}")
+        if out is None:
+            out = torch.empty((B, self.frames, self.n_mels), dtype=torch.float32, device=rt.device)
+        ws_bytes = lib.yoho_logmel_workspace_bytes(B, self.n_samples, self.n_fft, self.hop, self.n_mels)
+        ws = rt.workspace("logmel", ws_bytes)
+        fn = lib.yoho_logmel_s16 if pcm.dtype == torch.int16 else lib.yoho_logmel_f32
+        check(fn(rt.ctx, self.fb, C.c_void_p(pcm.data_ptr()), B, self.n_samples, self.n_fft, self.hop,
+                 C.c_void_p(out.data_ptr()), self.norm, C.c_void_p(rt.aligned_ptr(ws)), ws_bytes, rt.stream_ptr()))
+        return out
+
+    def encoder(self, mel: torch.Tensor, out: torch.Tensor | None = None, ws_tag: str = "encoder") -> torch.Tensor:
+        """(B, frames, n_mels) float32 CUDA tensor -> (B, seq_len, dims) float32, on the current stream."""
+        rt, lib = self.rt, self.rt.lib
+        B = mel.shape[0]
+        if out is None:
+            out = torch.empty((B, self.seq_len, self.dims), dtype=torch.float32, device=rt.device)
+        ws_bytes = lib.yoho_encoder_workspace_bytes(C.byref(self.desc), B, self.frames, self.compute)
+        ws = rt.workspace(ws_tag, ws_bytes)
+        check(lib.yoho_encoder_fwd(rt.ctx, C.byref(self.desc), C.c_void_p(rt.aligned_ptr(self.blob)), C.c_void_p(mel.data_ptr()),
+                                   B, self.frames, C.c_void_p(out.data_ptr()), self.compute,
+                                   C.c_void_p(rt.aligned_ptr(ws)), ws_bytes, rt.stream_ptr()))
+        return out
+
+    def encode(self, pcm: torch.Tensor, out: torch.Tensor | None = None, chunk_clips: int | None = None) -> torch.Tensor:
+        """PCM resident in HBM -> encoder states resident in HBM (current stream, no host sync)."""
+        B = pcm.shape[0]
+        if out is None:
+            out = torch.empty((B, self.seq_len, self.dims), dtype=torch.float32, device=self.rt.device)
+        step = B if not chunk_clips else max(1, min(int(chunk_clips), B))
+        with torch.cuda.device(self.rt.device):
+            for b0 in range(0, B, step):
+                b1 = min(B, b0 + step)
+                mel = self.logmel(pcm[b0:b1], self._mel_buf(b1 - b0))
+                self.encoder(mel, out[b0:b1])
+        return out
+
+    # ---- host-facing path -------------------------------------------------------------------
+    def host_buffers(self, batch: int, pcm_dtype: torch.dtype = torch.float32) -> tuple[torch.Tensor, torch.Tensor]:
+        """Pinned host buffers shaped for ``encode_host``: PCM (batch, n_samples) and states (batch, seq_len, dims)."""
+        return (torch.empty((batch, self.n_samples), dtype=pcm_dtype, pin_memory=True),
+                torch.empty((batch, self.seq_len, self.dims), dtype=torch.float32, pin_memory=True))
+
+    def encode_host(self, pcm_host: torch.Tensor, out_host: torch.Tensor | None = None, chunk_clips: int = 32,
+                    sync: bool = True) -> torch.Tensor:
+        """Host PCM -> host encoder states.  ``pcm_host``: CPU tensor / ndarray (B, n_samples), float32
+        or int16; pinned memory makes the H2D copies asynchronous (pageable memory still works, the
+        copies then serialise with the host).  Returns ``out_host`` (pinned unless supplied)."""
+        if isinstance(pcm_host, np.ndarray):
+            pcm_host = torch.from_numpy(np.ascontiguousarray(pcm_host))
+        B = pcm_host.shape[0]
+        if out_host is None:
+            out_host = torch.empty((B, self.seq_len, self.dims), dtype=torch.float32, pin_memory=True)
+        dev = self.rt.device
+        chunk = max(1, min(int(chunk_clips), B))
+        with torch.cuda.device(dev):
+            if self._streams is None:
+                self._streams = tuple(torch.cuda.Stream(device=dev) for _ in range(3))
+            s_in, s_run, s_out = self._streams
+            key = (chunk, pcm_host.dtype)
+            st = self._stage.get(key)
+            if st is None:
+                st = {"pcm": [torch.empty((chunk, self.n_samples), dtype=pcm_host.dtype, device=dev) for _ in range(2)],
+                      "out": [torch.empty((chunk, self.seq_len, self.dims), dtype=torch.float32, device=dev) for _ in range(2)]}
+                self._stage = {key: st}
+            entry = torch.cuda.current_stream(dev)
+            ready = torch.cuda.Event()
+            ready.record(entry)
+            for s in (s_in, s_run, s_out):
+                s.wait_event(ready)
+            ran: list = []
+            drained: list = []
+            for i, b0 in enumerate(range(0, B, chunk)):
+                b1 = min(B, b0 + chunk)
+                n, slot = b1 - b0, i & 1
+                with torch.cuda.stream(s_in):
+                    if i >= 2:
+                        s_in.wait_event(ran[i - 2])            # staging slot is free again
+                    st["pcm"][slot][:n].copy_(pcm_host[b0:b1], non_blocking=True)
+                    e_in = torch.cuda.Event()
+                    e_in.record(s_in)
+                with torch.cuda.stream(s_run):
+                    s_run.wait_event(e_in)
+                    if i >= 2:
+                        s_run.wait_event(drained[i - 2])
+                    mel = self.logmel(st["pcm"][slot][:n], self._mel_buf(n))
+                    self.encoder(mel, st["out"][slot][:n])
+                    e_run = torch.cuda.Event()
+                    e_run.record(s_run)
+                    ran.append(e_run)
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(e_run)
+                    out_host[b0:b1].copy_(st["out"][slot][:n], non_blocking=True)
+                    e_out = torch.cuda.Event()
+                    e_out.record(s_out)
+                    drained.append(e_out)
+            entry.wait_event(drained[-1])
+            entry.wait_event(ran[-1])
+            if sync:
+                drained[-1].synchronize()
+        return out_host
