@@ -122,4 +122,7 @@ def test_size_independent_properties_at_bench_size(api):
     assert n.mean(dim=(1, 2)).abs().max() < 1e-4 and (n.std(dim=(1, 2), unbiased=False) - 1).abs().max() < 1e-4
     w = api.log_mel_spectogram(x, norm="whisper")
     peak = w.amax(dim=(1, 2))
-    assert ((w.amin(dim=(1, 2)) - (peak - 2.0)).abs() < 1e-5).all()        # silent gap clamps at max - 8 -> (.. )/4 = peak - 2
+    # silent gap: log10 floor is -10 -> (-10+4)/4 = -1.5, unless the clamp at max-8 (-> peak - 2) is higher
+    floor = torch.maximum(peak - 2.0, torch.full_like(peak, -1.5))
+    assert ((w.amin(dim=(1, 2)) - floor).abs() < 1e-5).all()
+    assert (w >= floor[:, None, None] - 1e-6).all() and (w <= peak[:, None, None]).all()

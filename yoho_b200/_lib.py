@@ -29,6 +29,7 @@ _p, _i, _sz = C.c_void_p, C.c_int, C.c_size_t
 SIGNATURES = {
     "yoho_abi_version": (_i, []),
     "yoho_last_error": (C.c_char_p, []),
+    "yoho_xla_ffi_available": (_i, []),
     "yoho_ctx_create": (_i, [_i, C.POINTER(_p)]),
     "yoho_ctx_destroy": (_i, [_p]),
     "yoho_stft_frames": (_i, [_i, _i, _i]),

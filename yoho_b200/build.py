@@ -19,7 +19,7 @@ LIB_DIR = ROOT / "yoho_b200" / "lib"
 LIB = LIB_DIR / "libyoho_b200.so"
 OBJ_DIR = ROOT / "build" / "obj"
 
-SOURCES = ["api.cu", "frontend.cu", "elementwise.cu", "encoder_fp32.cu", "gemm_sm100.cu", "attention_sm100.cu", "encoder.cu"]
+SOURCES = ["api.cu", "frontend.cu", "elementwise.cu", "encoder_fp32.cu", "gemm_sm100.cu", "attention_sm100.cu", "encoder.cu", "xla_ffi.cc"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
@@ -43,7 +43,7 @@ def _digest(paths) -> str:
 
 
 def build(force: bool = False, verbose: bool = False) -> Path:
-    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cuh")) + [ROOT / "include" / "yoho_b200.h"]
+    deps = list(CSRC.glob("*.cu")) + list(CSRC.glob("*.cc")) + list(CSRC.glob("*.cuh")) + [ROOT / "include" / "yoho_b200.h"]
     stamp = LIB_DIR / ".build_digest"
     digest = _digest(deps)
     if not force and LIB.exists() and stamp.exists() and stamp.read_text() == digest:
