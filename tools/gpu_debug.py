@@ -178,6 +178,32 @@ def stage_perf():
         print(f"[perf] encoder {name} B={b} bf16: {ms:.2f} ms  {b * gf / ms:.1f} TFLOP/s  {b * 30 / ms * 1000:.0f}x realtime")
 
 
+def stage_gemmperf():
+    """Times the tcgen05 GEMM alone on the encoder's shapes (whisper-small, 64 clips = 96000 rows)."""
+    rt = get_runtime()
+    from yoho_b200 import _lib
+    lib = rt.lib
+    M = 96000
+    for (name, n, k, epi) in [("qkv", 2304, 768, 0), ("out", 768, 768, 0), ("fc1", 3072, 768, 1), ("fc2", 768, 3072, 0), ("conv0", 768, 256, 1)]:
+        a = torch.randn((M, k), device="cuda")
+        w = torch.randn((k, n), device="cuda") / k ** 0.5
+        bias = torch.randn(n, device="cuda")
+        out = torch.empty((M, n), device="cuda")
+        nbytes = lib.yoho_test_gemm_workspace_bytes(M, n, k)
+        ws = rt.workspace("test", nbytes)
+        lib.yoho_prof_enable(1)
+        for _ in range(6):
+            check(lib.yoho_test_gemm_bf16(rt.ctx, C.c_void_p(a.data_ptr()), C.c_void_p(w.data_ptr()), C.c_void_p(bias.data_ptr()),
+                                          C.c_void_p(out.data_ptr()), M, n, k, epi, C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
+        torch.cuda.synchronize()
+        ncls = lib.yoho_prof_num_classes()
+        ms, work, cnt = (C.c_double * ncls)(), (C.c_double * ncls)(), (C.c_longlong * ncls)()
+        check(lib.yoho_prof_collect(ms, work, cnt, ncls))
+        lib.yoho_prof_enable(0)
+        g = 2  # gemm_tcgen05 class
+        print(f"[gemmperf] {name:6s} M={M} N={n} K={k}: {ms[g] / cnt[g] * 1e3:8.1f} us  {work[g] / ms[g] / 1e9:7.1f} TFLOP/s (f32 out; avg of {cnt[g]})")
+
+
 if __name__ == "__main__":
     torch.cuda.init()
     print("device:", torch.cuda.get_device_name(0))
