@@ -111,9 +111,11 @@ def stage_gemm():
 
 def stage_attention():
     rt = get_runtime()
-    for (batch, t, heads) in [(1, 128, 1), (1, 256, 1), (2, 100, 2), (1, 1500, 2)]:
+    for (batch, t, heads, scale) in [(1, 128, 1, 1.0), (1, 256, 1, 1.0), (2, 100, 2, 1.0), (1, 64, 1, 1.0), (2, 192, 2, 1.0), (3, 700, 3, 1.0),
+                                     (1, 1500, 2, 1.0), (2, 1500, 2, 3.0), (200, 300, 3, 1.0)]:
         rng = np.random.default_rng(t + heads)
         qkv = rng.standard_normal((batch, t, 3, heads, 64)).astype(np.float32)
+        qkv[:, :, :2] *= scale          # scale > 1: score spread far beyond 2^8, exercises the lazy O rescale
         r = bf16(qkv).astype(np.float64)
         q, k, v = (r[:, :, i].transpose(0, 2, 1, 3) for i in range(3))
         s = q @ k.transpose(0, 1, 3, 2) / 8.0
@@ -129,7 +131,7 @@ def stage_attention():
         torch.cuda.synchronize()
         got = out.cpu().numpy()
         err = np.abs(got - want)
-        print(f"[attention] B{batch} T{t} H{heads}: max err {np.nanmax(err):.3e} nan {int((~np.isfinite(got)).sum())} (max|o| {np.abs(want).max():.2f})")
+        print(f"[attention] B{batch} T{t} H{heads} x{scale}: max err {np.nanmax(err):.3e} nan {int((~np.isfinite(got)).sum())} (max|o| {np.abs(want).max():.2f})")
         if np.nanmax(err) > 3e-2:
             vmean = v.mean(axis=2)  # uniform softmax would give this
             print("[attention]   err vs uniform-softmax:", np.abs(got[0, :, :64] - vmean[0, 0]).max())
@@ -202,6 +204,31 @@ def stage_gemmperf():
         lib.yoho_prof_enable(0)
         g = 2  # gemm_tcgen05 class
         print(f"[gemmperf] {name:6s} M={M} N={n} K={k}: {ms[g] / cnt[g] * 1e3:8.1f} us  {work[g] / ms[g] / 1e9:7.1f} TFLOP/s (f32 out; avg of {cnt[g]})")
+
+
+def stage_attnperf():
+    """Times the tcgen05 attention kernel alone (whisper-small heads, 64 clips)."""
+    rt = get_runtime()
+    lib = rt.lib
+    for (batch, t, heads) in [(64, 1500, 12), (64, 1536, 12), (16, 1500, 20)]:
+        qkv = torch.randn((batch, t, 3, heads, 64), device="cuda")
+        out = torch.empty((batch, t, heads * 64), device="cuda")
+        nbytes = lib.yoho_test_attention_workspace_bytes(batch, t, heads)
+        ws = rt.workspace("test", nbytes)
+        lib.yoho_prof_enable(1)
+        for _ in range(5):
+            check(lib.yoho_test_attention_bf16(rt.ctx, C.c_void_p(qkv.data_ptr()), C.c_void_p(out.data_ptr()), batch, t, heads,
+                                               C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
+        torch.cuda.synchronize()
+        ncls = lib.yoho_prof_num_classes()
+        ms, work, cnt = (C.c_double * ncls)(), (C.c_double * ncls)(), (C.c_longlong * ncls)()
+        check(lib.yoho_prof_collect(ms, work, cnt, ncls))
+        lib.yoho_prof_enable(0)
+        a = 3
+        tiles = batch * heads * ((t + 127) // 128) ** 2
+        us = ms[a] / cnt[a] * 1e3
+        print(f"[attnperf] B{batch} T{t} H{heads}: {us:8.1f} us  {work[a] / ms[a] / 1e9:7.1f} TFLOP/s  "
+              f"{us * 1e-6 * 1.9e9 * 148 / tiles:6.0f} SM-cycles@1.9GHz per 128x128 tile pair")
 
 
 if __name__ == "__main__":

@@ -2,20 +2,21 @@
 //   out = softmax(q k^T / sqrt(64)) v   per (clip, head), no mask      (reference whisper.py:52-67)
 // The reference materialises the (B, H, 1500, 1500) score tensor; here scores never leave the SM.
 //
-// Persistent kernel, one CTA per SM, 10 warps.  A work item is (clip, head, 256 query rows) = two
-// 128-row query tiles A and B that share every K/V tile:
+// Persistent kernel, one CTA per SM, 11 warps.  A work item is (clip, head, 256 query rows) = two
+// 128-row query tiles A and B that share every K/V tile; a step is 64 keys of an item:
 //   warps 0-3  softmax of tile A   (thread i owns query row i = TMEM lane i: row max / sum need no shuffles)
 //   warps 4-7  softmax of tile B
-//   warp 8     TMA producer: Q tiles (double buffered across items), K_j / V_j rings of 128 keys
-//   warp 9     MMA issuer + TMEM allocator
-// Per KV tile j and query tile t:  S_t = Q_t K_j^T (M128 N128 K64, operands in shared memory)
-//                                  O_t += P_t V_j  (M128 N64 K128, P read from TMEM, V MN-major from its TMA tile)
-// TMEM: S_A | S_B (128 fp32 columns each), O_A | O_B (64 columns each).  The softmax threads read S twice
-// (row max, then exp2), write P as packed bf16 over the first 64 columns of S (tcgen05.st) and keep the row
-// sum in registers.  O stays in TMEM across KV tiles: it is only rescaled when the running maximum
-// grows by more than 2^8 (lazy rescaling; P is then bounded by 256), so the common case has no correction.
-// While one tile's softmax runs on the SFU (16 ex2/clk/SM is the bound at d_head = 64), the tensor core
-// runs the other tile's MMAs.  Keys past the clip end are TMA zero-filled and masked to -inf.
+//   warp 8     TMA producer: Q tiles (double buffered across items), K_j / V_j rings of 128 keys (= 2 steps)
+//   warp 9/10  MMA issuer of tile A / tile B (warp 9 also allocates TMEM)
+// Per step g and query tile t:  S_t[g&1] = Q_t K_g^T (M128 N64 K64, operands in shared memory) -- issued 2 steps ahead
+//                               O_t += P_t V_g        (M128 N64 K64, P read from TMEM, V MN-major from its TMA tile)
+// TMEM: S_t[b] = 64 fp32 columns at 128 t + 64 b, O_t = 64 columns at 256 + 64 t.  S is double buffered per
+// query tile so that Q K^T of step g+1 is already in TMEM when the softmax of step g retires: the softmax warps
+// never wait for the tensor core, only for the SFU (16 ex2/clk/SM is the bound at d_head = 64).  A softmax
+// thread reads its 64 scores once, takes the row maximum, writes P as packed bf16 over the first 32 columns of
+// the same S buffer (tcgen05.st) and keeps the row sum in registers.  O stays in TMEM across steps: it is
+// only rescaled when the running maximum grows by more than 2^8 (lazy rescaling; P is then bounded by 256), so
+// the common case has no correction.  Keys past the clip end are TMA zero-filled and masked to -inf.
 #include "kernels.cuh"
 #include "ptx_sm100.cuh"
 
@@ -23,13 +24,13 @@ namespace yoho {
 
 using namespace ptx;
 
-constexpr int kAttThreads = 320;
-constexpr int kTileQ = 128, kTileKV = 128, kHeadDim = 64;
+constexpr int kAttThreads = 352;
+constexpr int kTileQ = 128, kTileKV = 128, kStepKV = 64, kHeadDim = 64;
 constexpr int kItemQ = 2 * kTileQ;        // query rows per work item
 constexpr int kTileBytes = 128 * 64 * 2;  // one (128 rows x 64 bf16) swizzled tile = 16 KB
 constexpr int kKvStages = 4;
 constexpr uint32_t kAttTmemCols = 512;
-constexpr uint32_t kTmemS = 0, kTmemO = 256;   // S_t at kTmemS + 128 t, O_t at kTmemO + 64 t
+constexpr uint32_t kTmemS = 0, kTmemO = 256;   // S_t[b] at kTmemS + 128 t + 64 b, O_t at kTmemO + 64 t
 constexpr float kRescaleLog2 = 8.0f;
 
 struct AttSmem {
@@ -38,7 +39,8 @@ struct AttSmem {
   unsigned char v[kKvStages][kTileBytes];
   uint64_t q_full[2][2], q_empty[2][2];
   uint64_t k_full[kKvStages], k_empty[kKvStages], v_full[kKvStages], v_empty[kKvStages];
-  uint64_t s_full[2], p_full[2], o_full[2];
+  uint64_t s_full[2][2], p_full[2][2];   // [query tile][S buffer]
+  uint64_t o_full[2], o_last[2], o_free[2];   // [query tile]: every P V / last P V of an item / O read out
   uint32_t tmem_slot;
 };
 
@@ -46,7 +48,8 @@ struct AttParams {
   int t_len, dims, heads;
   int q_blocks;      // ceil(t_len / 256)
   int n_items;       // batch * heads * q_blocks
-  int n_kv;          // ceil(t_len / 128)
+  int n_kv;          // ceil(t_len / 128): K/V tiles per item
+  int n_steps;       // ceil(t_len / 64): softmax steps per item
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -60,69 +63,6 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
   return y;
 }
 
-// Row maximum of one 128-column S tile (this thread's TMEM lane); columns >= kv_valid are ignored when kMask.
-template <bool kMask>
-__device__ __forceinline__ float tile_row_max(uint32_t s_addr, int kv_valid) {
-  float m = -INFINITY;
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    uint32_t a[32], b[32];
-    tmem_ld_32x32b_x32(s_addr + h * 64, a);
-    tmem_ld_32x32b_x32(s_addr + h * 64 + 32, b);
-    tmem_ld_wait();
-#pragma unroll
-    for (int i = 0; i < 32; i += 2) {
-      float x0 = __uint_as_float(a[i]), x1 = __uint_as_float(a[i + 1]);
-      float y0 = __uint_as_float(b[i]), y1 = __uint_as_float(b[i + 1]);
-      if (kMask) {
-        if (h * 64 + i >= kv_valid) x0 = -INFINITY;
-        if (h * 64 + i + 1 >= kv_valid) x1 = -INFINITY;
-        if (h * 64 + 32 + i >= kv_valid) y0 = -INFINITY;
-        if (h * 64 + 32 + i + 1 >= kv_valid) y1 = -INFINITY;
-      }
-      m = fmax3(m, x0, x1);
-      m = fmax3(m, y0, y1);
-    }
-  }
-  return m;
-}
-
-// p = exp2(s c - mc) for the 128 columns of this thread's row; P is written as packed bf16 over the first 64
-// columns of the S tile (columns already consumed); returns the row sum of the unrounded p.
-template <bool kMask>
-__device__ __forceinline__ float tile_exp_store(uint32_t s_addr, float c, float mc, int kv_valid) {
-  float l0 = 0.0f, l1 = 0.0f;
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    uint32_t a[32], b[32];
-    tmem_ld_32x32b_x32(s_addr + h * 64, a);
-    tmem_ld_32x32b_x32(s_addr + h * 64 + 32, b);
-    tmem_ld_wait();
-    uint32_t packed[32];
-#pragma unroll
-    for (int i = 0; i < 32; i += 2) {
-      float p0 = ex2_approx(fmaf(__uint_as_float(a[i]), c, -mc));
-      float p1 = ex2_approx(fmaf(__uint_as_float(a[i + 1]), c, -mc));
-      float r0 = ex2_approx(fmaf(__uint_as_float(b[i]), c, -mc));
-      float r1 = ex2_approx(fmaf(__uint_as_float(b[i + 1]), c, -mc));
-      if (kMask) {
-        if (h * 64 + i >= kv_valid) p0 = 0.0f;
-        if (h * 64 + i + 1 >= kv_valid) p1 = 0.0f;
-        if (h * 64 + 32 + i >= kv_valid) r0 = 0.0f;
-        if (h * 64 + 32 + i + 1 >= kv_valid) r1 = 0.0f;
-      }
-      l0 += p0 + p1;
-      l1 += r0 + r1;
-      __nv_bfloat162 u = __floats2bfloat162_rn(p0, p1), w = __floats2bfloat162_rn(r0, r1);
-      packed[i >> 1] = *reinterpret_cast<uint32_t*>(&u);          // keys h*64 + i, i+1
-      packed[16 + (i >> 1)] = *reinterpret_cast<uint32_t*>(&w);   // keys h*64 + 32 + i, i+1
-    }
-    tmem_st_32x32b_x32(s_addr + h * 32, packed);                  // P columns h*32 .. +31 = keys h*64 .. +63
-  }
-  tmem_st_wait();
-  return l0 + l1;
-}
-
 __global__ void __launch_bounds__(kAttThreads, 1)
 attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, const AttParams p) {
   extern __shared__ __align__(1024) unsigned char att_smem_raw[];
@@ -134,10 +74,13 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
     for (int s = 0; s < 2; ++s)
       for (int t = 0; t < 2; ++t) { mbar_init(&sm.q_full[s][t], 1); mbar_init(&sm.q_empty[s][t], 1); }
     for (int i = 0; i < kKvStages; ++i) {
-      mbar_init(&sm.k_full[i], 1); mbar_init(&sm.k_empty[i], 1);
-      mbar_init(&sm.v_full[i], 1); mbar_init(&sm.v_empty[i], 1);
+      mbar_init(&sm.k_full[i], 1); mbar_init(&sm.k_empty[i], 2);   // released by both MMA warps
+      mbar_init(&sm.v_full[i], 1); mbar_init(&sm.v_empty[i], 2);
     }
-    for (int t = 0; t < 2; ++t) { mbar_init(&sm.s_full[t], 1); mbar_init(&sm.p_full[t], 4); mbar_init(&sm.o_full[t], 1); }
+    for (int t = 0; t < 2; ++t) {
+      for (int b = 0; b < 2; ++b) { mbar_init(&sm.s_full[t][b], 1); mbar_init(&sm.p_full[t][b], 4); }
+      mbar_init(&sm.o_full[t], 1); mbar_init(&sm.o_last[t], 1); mbar_init(&sm.o_free[t], 4);
+    }
     fence_mbar_init();
   }
   if (warp == 8 && lane == 0) prefetch_tmap(&map_qkv);
@@ -149,14 +92,16 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = sm.tmem_slot;
-  const int n_kv = p.n_kv;
+  const int n_kv = p.n_kv, n_steps = p.n_steps;
+  const int stride = int(gridDim.x);
+  const int n_my = int(blockIdx.x) < p.n_items ? (p.n_items - int(blockIdx.x) + stride - 1) / stride : 0;   // items of this CTA
 
   if (warp == 8) {
     // ===================== TMA producer (one lane) =====================
     if (lane == 0) {
       int kc = 0;   // K/V tiles issued so far (ring position)
-      int it = 0;
-      for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
+      for (int it = 0; it < n_my; ++it) {
+        const int item = int(blockIdx.x) + it * stride;
         const int qb = item % p.q_blocks, ch = item / p.q_blocks;
         const int head = ch % p.heads, clip = ch / p.heads;
         const int slot = it & 1; const uint32_t qph = (it >> 1) & 1;
@@ -177,73 +122,64 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
       }
     }
     __syncwarp();
-  } else if (warp == 9) {
-    // ===================== MMA issuer (one lane) =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc_qk = make_idesc_bf16(kTileQ, kTileKV, 0, 0);   // A = Q (K-major), B = K (K-major)
-      constexpr uint32_t idesc_pv = make_idesc_bf16(kTileQ, kHeadDim, 0, 1);  // A = P (TMEM), B = V (MN-major)
-      int kq = 0;   // K tiles consumed by QK so far (ring position of the NEXT QK)
-      int kv = 0;   // V tiles consumed by PV so far
-      int g = 0;    // KV steps completed (phase of s_full / p_full / o_full)
-      // S_t = Q_t K^T for the K tile at ring position kq; releases the K slot after tile B.
-      auto issue_qk = [&](int t, int slot, bool last_of_item) {
-        const int st = kq % kKvStages;
-        if (t == 0) { mbar_wait(&sm.k_full[st], (kq / kKvStages) & 1); }
-        tc_fence_after();
-        const uint64_t adesc = make_desc_sw128(smem_u32(sm.q[slot][t]), 16, 1024);
-        const uint64_t bdesc = make_desc_sw128(smem_u32(sm.k[st]), 16, 1024);
+  } else if (warp >= 9) {
+    // ===================== MMA issuers: warp 9 = query tile A, warp 10 = query tile B =====================
+    // The whole warp stays converged and one elected lane issues (umma_*_w).  Every MMA here is small (M128 N64 K16
+    // = 32 tensor-pipe cycles), so the issuing instruction stream is kept short: shared-memory descriptors are
+    // linear in (ring stage, half, k step) and advanced by constant adds, ring positions are carried, not divided.
+    const int t = warp - 9;
+    constexpr uint32_t idesc_qk = make_idesc_bf16(kTileQ, kStepKV, 0, 0);   // A = Q (K-major), B = K (K-major)
+    constexpr uint32_t idesc_pv = make_idesc_bf16(kTileQ, kHeadDim, 0, 1);  // A = P (TMEM), B = V (MN-major)
+    constexpr uint64_t kStageDesc = kTileBytes >> 4, kHalfDesc = (kStepKV * 128) >> 4;
+    const uint64_t qdesc0 = make_desc_sw128(smem_u32(sm.q[0][t]), 16, 1024);       // slot s: + 2 s kStageDesc
+    const uint64_t kdesc0 = make_desc_sw128(smem_u32(sm.k[0]), 16, 1024);          // stage st: + st kStageDesc
+    const uint64_t vdesc0 = make_desc_sw128(smem_u32(sm.v[0]), 1024, 1024);
+    const uint32_t s_tmem = tmem_base + kTmemS + uint32_t(t * 128), o_tmem = tmem_base + kTmemO + uint32_t(t * 64);
+    const int g_total = n_my * n_steps;
+    // Q K^T cursor (runs two steps ahead of P V)
+    int q_it = 0, q_j = 0, q_st = 0; uint32_t q_ph = 0;
+    auto issue_qk = [&](int g) {
+      const int sb = g & 1, half = q_j & 1;
+      const bool last = q_j == n_steps - 1;
+      if (q_j == 0) mbar_wait(&sm.q_full[q_it & 1][t], (q_it >> 1) & 1);
+      mbar_wait(&sm.k_full[q_st], q_ph);
+      tc_fence_after();
+      const uint64_t adesc = qdesc0 + uint64_t(q_it & 1) * (2 * kStageDesc);
+      const uint64_t bdesc = kdesc0 + uint64_t(q_st) * kStageDesc + uint64_t(half) * kHalfDesc;
+      const uint32_t d = s_tmem + uint32_t(sb * 64);
 #pragma unroll
-        for (int k = 0; k < kHeadDim / 16; ++k)
-          umma_bf16_ss(tmem_base + kTmemS + uint32_t(t * 128), adesc + uint64_t(2 * k), bdesc + uint64_t(2 * k), idesc_qk, k != 0);
-        umma_commit(&sm.s_full[t]);
-        if (last_of_item) umma_commit(&sm.q_empty[slot][t]);
-        if (t == 1) { umma_commit(&sm.k_empty[st]); ++kq; }
-      };
-      auto issue_pv = [&](int t, int j) {
-        const int st = kv % kKvStages;
-        mbar_wait(&sm.p_full[t], g & 1);      // P_t in TMEM, S_t consumed, O_t rescaled if needed
-        if (t == 0) mbar_wait(&sm.v_full[st], (kv / kKvStages) & 1);
-        tc_fence_after();
-        const uint32_t v_addr = smem_u32(sm.v[st]);
+      for (int k = 0; k < kHeadDim / 16; ++k) umma_bf16_ss_w(d, adesc + uint64_t(2 * k), bdesc + uint64_t(2 * k), idesc_qk, k != 0);
+      umma_commit_w(&sm.s_full[t][sb]);
+      if (last) umma_commit_w(&sm.q_empty[q_it & 1][t]);
+      if (half == 1 || last) {
+        umma_commit_w(&sm.k_empty[q_st]);
+        if (++q_st == kKvStages) { q_st = 0; q_ph ^= 1; }
+      }
+      if (last) { q_j = 0; ++q_it; } else { ++q_j; }
+    };
+    for (int g = 0; g < 2 && g < g_total; ++g) issue_qk(g);
+    int p_it = 0, p_j = 0, p_st = 0; uint32_t p_ph = 0;
+    for (int g = 0; g < g_total; ++g) {
+      const int sb = g & 1, half = p_j & 1;
+      const bool last = p_j == n_steps - 1;
+      mbar_wait(&sm.p_full[t][sb], (g >> 1) & 1);                        // P in TMEM, S consumed, O rescaled if needed
+      if (p_j == 0 && p_it > 0) mbar_wait(&sm.o_free[t], (p_it - 1) & 1);  // previous item's O has been read out
+      mbar_wait(&sm.v_full[p_st], p_ph);
+      tc_fence_after();
+      // A: 16 keys = 8 packed columns.  B: V rows are keys (128 B each): 16 keys = 2 groups of 8 rows, 1024 B apart
+      const uint64_t bdesc = vdesc0 + uint64_t(p_st) * kStageDesc + uint64_t(half) * kHalfDesc;
+      const uint32_t p_addr = s_tmem + uint32_t(sb * 64);
 #pragma unroll
-        for (int ks = 0; ks < kTileKV / 16; ++ks) {
-          // B: V rows are keys (128 B each): 16 keys = 2 groups of 8 rows, 1024 B apart
-          const uint64_t bdesc = make_desc_sw128(v_addr + ks * 2048, 1024, 1024);
-          umma_bf16_ts(tmem_base + kTmemO + uint32_t(t * 64), tmem_base + kTmemS + uint32_t(t * 128 + ks * 8), bdesc, idesc_pv,
-                       (j | ks) != 0);
-        }
-        umma_commit(&sm.o_full[t]);
-        if (t == 1) { umma_commit(&sm.v_empty[st]); ++kv; }
-      };
-      int it = 0;
-      const int first = blockIdx.x;
-      if (first < p.n_items) {
-        mbar_wait(&sm.q_full[0][0], 0);
-        issue_qk(0, 0, n_kv == 1);
-        mbar_wait(&sm.q_full[0][1], 0);
-        issue_qk(1, 0, n_kv == 1);
+      for (int ks = 0; ks < kStepKV / 16; ++ks)
+        umma_bf16_ts_w(o_tmem, p_addr + uint32_t(ks * 8), bdesc + uint64_t(ks * (2048 >> 4)), idesc_pv, (p_j | ks) != 0);
+      umma_commit_w(&sm.o_full[t]);
+      if (last) umma_commit_w(&sm.o_last[t]);
+      if (half == 1 || last) {
+        umma_commit_w(&sm.v_empty[p_st]);
+        if (++p_st == kKvStages) { p_st = 0; p_ph ^= 1; }
       }
-      for (int item = first; item < p.n_items; item += gridDim.x, ++it) {
-        const int slot = it & 1;
-        const bool has_next_item = item + int(gridDim.x) < p.n_items;
-        const int nslot = (it + 1) & 1; const uint32_t nqph = ((it + 1) >> 1) & 1;
-        for (int j = 0; j < n_kv; ++j, ++g) {
-          const bool in_item = j + 1 < n_kv;
-          const bool next = in_item || has_next_item;
-          const int qslot = in_item ? slot : nslot;
-          const bool next_last = in_item ? (j + 2 == n_kv) : (n_kv == 1);
-          issue_pv(0, j);
-          if (next) {
-            if (!in_item) mbar_wait(&sm.q_full[nslot][0], nqph);
-            issue_qk(0, qslot, next_last);
-          }
-          issue_pv(1, j);
-          if (next) {
-            if (!in_item) mbar_wait(&sm.q_full[nslot][1], nqph);
-            issue_qk(1, qslot, next_last);
-          }
-        }
-      }
+      if (last) { p_j = 0; ++p_it; } else { ++p_j; }
+      if (g + 2 < g_total) issue_qk(g + 2);
     }
     __syncwarp();
   } else {
@@ -251,20 +187,41 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
     const int t = warp >> 2;
     const int row = (warp & 3) * 32 + lane;                   // query row in the tile == TMEM lane
     const uint32_t lane_base = tmem_base + (uint32_t((warp & 3) * 32) << 16);
-    const uint32_t s_addr = lane_base + kTmemS + uint32_t(t * 128);
+    const uint32_t s_base = lane_base + kTmemS + uint32_t(t * 128);
     const uint32_t o_addr = lane_base + kTmemO + uint32_t(t * 64);
     const float c = 0.125f * 1.4426950408889634f;            // d_head^-0.5 * log2(e)   (whisper.py:54-57)
-    const int kv_tail = p.t_len - (n_kv - 1) * kTileKV;       // valid keys of the last KV tile
+    const int kv_tail = p.t_len - (n_steps - 1) * kStepKV;    // valid keys of the last step
     int g = 0;
-    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+    for (int it = 0; it < n_my; ++it) {
+      const int item = int(blockIdx.x) + it * stride;
       const int qb = item % p.q_blocks, ch = item / p.q_blocks;
       const int head = ch % p.heads, clip = ch / p.heads;
       float m_ref = -INFINITY, l_run = 0.0f;
-      for (int j = 0; j < n_kv; ++j, ++g) {
-        const bool tail = (j == n_kv - 1) && kv_tail < kTileKV;   // CTA-uniform
-        mbar_wait(&sm.s_full[t], g & 1);
+      for (int j = 0; j < n_steps; ++j, ++g) {
+        const int sb = g & 1;
+        const uint32_t s_addr = s_base + uint32_t(sb * 64);
+        mbar_wait(&sm.s_full[t][sb], (g >> 1) & 1);
         tc_fence_after();
-        const float m_tile = tail ? tile_row_max<true>(s_addr, kv_tail) : tile_row_max<false>(s_addr, kv_tail);
+        uint32_t a[32], b[32];
+        tmem_ld_32x32b_x32(s_addr, a);
+        tmem_ld_32x32b_x32(s_addr + 32, b);
+        tmem_ld_wait();
+        if (j == n_steps - 1 && kv_tail < kStepKV) {          // CTA-uniform
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            if (i >= kv_tail) a[i] = 0xff800000u;               // -inf: exp2 gives exactly 0
+            if (32 + i >= kv_tail) b[i] = 0xff800000u;
+          }
+        }
+        float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          m0 = fmax3(m0, __uint_as_float(a[i]), __uint_as_float(a[i + 1]));
+          m1 = fmax3(m1, __uint_as_float(a[i + 2]), __uint_as_float(a[i + 3]));
+          m2 = fmax3(m2, __uint_as_float(b[i]), __uint_as_float(b[i + 1]));
+          m3 = fmax3(m3, __uint_as_float(b[i + 2]), __uint_as_float(b[i + 3]));
+        }
+        const float m_tile = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
         if (j == 0) {
           m_ref = m_tile;
         } else if (__any_sync(0xffffffffu, (m_tile - m_ref) * c > kRescaleLog2)) {
@@ -273,7 +230,7 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
           const float alpha = ex2_approx((m_ref - m_new) * c);
           m_ref = m_new;
           l_run *= alpha;
-          mbar_wait(&sm.o_full[t], (g - 1) & 1);                  // P V of the previous KV tile has landed in O
+          mbar_wait(&sm.o_full[t], (g - 1) & 1);                  // P V of the previous step has landed in O
           tc_fence_after();
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
@@ -287,38 +244,57 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
           tmem_st_wait();
         }
         const float mc = m_ref * c;
-        l_run += tail ? tile_exp_store<true>(s_addr, c, mc, kv_tail) : tile_exp_store<false>(s_addr, c, mc, kv_tail);
+        float l0 = 0.0f, l1 = 0.0f, l2 = 0.0f, l3 = 0.0f;
+        uint32_t packed[32];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          const float p0 = ex2_approx(fmaf(__uint_as_float(a[i]), c, -mc));
+          const float p1 = ex2_approx(fmaf(__uint_as_float(a[i + 1]), c, -mc));
+          const float r0 = ex2_approx(fmaf(__uint_as_float(b[i]), c, -mc));
+          const float r1 = ex2_approx(fmaf(__uint_as_float(b[i + 1]), c, -mc));
+          l0 += p0; l1 += p1; l2 += r0; l3 += r1;
+          __nv_bfloat162 u = __floats2bfloat162_rn(p0, p1), w = __floats2bfloat162_rn(r0, r1);
+          packed[i >> 1] = *reinterpret_cast<uint32_t*>(&u);          // keys i, i+1
+          packed[16 + (i >> 1)] = *reinterpret_cast<uint32_t*>(&w);   // keys 32 + i, i+1
+        }
+        l_run += (l0 + l1) + (l2 + l3);
+        tmem_st_32x32b_x32(s_addr, packed);      // P over the first 32 (already consumed) columns of this S buffer
+        tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.p_full[t]);
+        if (lane == 0) mbar_arrive(&sm.p_full[t][sb]);
       }
-      // last P V of the item, normalise, store
-      mbar_wait(&sm.o_full[t], (g - 1) & 1);
+      // last P V of the item: pull O into registers, hand O_t back to the MMA warp, then normalise and store.
+      // (o_full cannot be used here: the softmax may be two P V commits ahead, and a parity wait only tells the
+      // current phase from the previous one.  In the rescale path above s_full(g) implies P V(g-2) has retired.)
+      mbar_wait(&sm.o_last[t], it & 1);
       tc_fence_after();
+      uint32_t o0[32], o1[32];
+      tmem_ld_32x32b_x32(o_addr, o0);
+      tmem_ld_32x32b_x32(o_addr + 32, o1);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.o_free[t]);
       const float inv_l = 1.0f / l_run;
       const int t_row = qb * kItemQ + t * kTileQ + row;
-      __nv_bfloat16* dst = out + (size_t(clip) * p.t_len + t_row) * p.dims + head * kHeadDim;
+      if (t_row < p.t_len) {
+        __nv_bfloat16* dst = out + (size_t(clip) * p.t_len + t_row) * p.dims + head * kHeadDim;
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        uint32_t o[32];
-        tmem_ld_32x32b_x32(o_addr + h * 32, o);
-        tmem_ld_wait();
-        if (t_row < p.t_len) {
+        for (int q4 = 0; q4 < 4; ++q4) {
+          uint32_t w0[4], w1[4];
 #pragma unroll
-          for (int q4 = 0; q4 < 4; ++q4) {
-            uint32_t w[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int i = q4 * 8 + e * 2;
-              __nv_bfloat162 hh = __floats2bfloat162_rn(__uint_as_float(o[i]) * inv_l, __uint_as_float(o[i + 1]) * inv_l);
-              w[e] = *reinterpret_cast<uint32_t*>(&hh);
-            }
-            *reinterpret_cast<uint4*>(dst + h * 32 + q4 * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+          for (int e = 0; e < 4; ++e) {
+            const int i = q4 * 8 + e * 2;
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(__uint_as_float(o0[i]) * inv_l, __uint_as_float(o0[i + 1]) * inv_l);
+            __nv_bfloat162 h1 = __floats2bfloat162_rn(__uint_as_float(o1[i]) * inv_l, __uint_as_float(o1[i + 1]) * inv_l);
+            w0[e] = *reinterpret_cast<uint32_t*>(&h0);
+            w1[e] = *reinterpret_cast<uint32_t*>(&h1);
           }
+          *reinterpret_cast<uint4*>(dst + q4 * 8) = make_uint4(w0[0], w0[1], w0[2], w0[3]);
+          *reinterpret_cast<uint4*>(dst + 32 + q4 * 8) = make_uint4(w1[0], w1[1], w1[2], w1[3]);
         }
       }
-      // O_t / S_t are overwritten by the next item's MMAs only after this warp arrives on p_full again
-      tc_fence_before();
     }
   }
 
@@ -335,6 +311,7 @@ int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16
   p.t_len = t; p.dims = dims; p.heads = heads;
   p.q_blocks = ceil_div(t, kItemQ);
   p.n_kv = ceil_div(t, kTileKV);
+  p.n_steps = ceil_div(t, kStepKV);
   const long long items = (long long)batch * heads * p.q_blocks;
   if (items > 0x7fffffffLL) return fail(YOHO_ERR_UNSUPPORTED, "attention: %lld work items", items);
   p.n_items = int(items);
