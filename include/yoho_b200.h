@@ -61,7 +61,7 @@ typedef enum yoho_compute {
 int yoho_abi_version(void);
 const char* yoho_last_error(void);
 /* 1 when the library was built with the XLA FFI headers and exports the jax.ffi handler symbols
- * yoho_xla_logmel / yoho_xla_normalize / yoho_xla_encoder (csrc/xla_ffi.cc); else 0. */
+ * yoho_xla_logmel / yoho_xla_normalize / yoho_xla_encoder - see csrc/xla_ffi.cc and INTEGRATION.md; else 0. */
 int yoho_xla_ffi_available(void);
 
 /* Creates the per-device state (FFT twiddles, window, driver entry points).  May allocate
