@@ -326,7 +326,19 @@ def main():
                            "launches_per_step": n / args.steps, "ms_per_step": round(cms / args.steps, 4),
                            "share_of_step": round(cms / ms_total, 4)}
     dominant = max(rooflines, key=lambda k: rooflines[k]["ms_per_step"]) if rooflines else None
-    roofline = dict(rooflines[dominant], kernel=dominant, traffic=None,
+    # DRAM bytes per launch of the dominant kernel, from the committed `ncu --set full` capture (profiles/traffic.json,
+    # written by tools/ncu_traffic.py from a 32-clip run of the same kernels), scaled to this run's clips per launch.
+    traffic, traffic_note = None, "no profiles/traffic.json"
+    try:
+        tj = json.loads((ROOT / "profiles" / "traffic.json").read_text())
+        if dominant in tj:
+            per_launch_clips = B if dominant != "logmel" else B / max(1.0, rooflines[dominant]["launches_per_step"])
+            traffic = round(tj[dominant]["bytes_per_launch_per_clip"] * per_launch_clips)
+            traffic_note = (f"ncu dram__bytes_read.sum + dram__bytes_write.sum, mean of {tj[dominant]['launches']} launch(es) at "
+                            f"{tj[dominant]['clips']} clips, scaled to {per_launch_clips:.0f} clips per launch")
+    except Exception as exc:
+        traffic_note = f"profiles/traffic.json unreadable: {exc!r}"
+    roofline = dict(rooflines[dominant], kernel=dominant, traffic=traffic, traffic_note=traffic_note,
                     peak_source=f"{pk['source']} ({'sustained bf16 cuBLAS' if rooflines[dominant]['bound'] == 'tensor' else 'copy bandwidth'}, MEASURED_PEAKS.json)") if dominant else None
 
     if rank != 0:
