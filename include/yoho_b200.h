@@ -160,6 +160,44 @@ int yoho_encoder_fwd(yoho_ctx* ctx, const yoho_enc_desc* desc, const void* blob,
                      int batch, int frames, float* out, int compute, void* ws, size_t ws_bytes,
                      yoho_stream_t stream);
 
+/* ---- YOHO's own audio encoder (next row after the Whisper path) ------------------------ */
+
+/* Shape of AudioEncoder(q_heads, kv_heads, dims, seq_len, blocks) (yoho/src/nn/model.py:9-14) plus the mel
+ * width of its input; Model.setup builds it with kv_heads = n_audio_heads // 2 (model.py:60-66).
+ * dims / q_heads must be 64 and n_mels a multiple of 64 (the reference config: 384 / 6, 128 mels). */
+typedef struct yoho_model_desc {
+  int32_t n_mels;   /* input channels of Conv_0                              */
+  int32_t dims;     /* D                                                      */
+  int32_t q_heads;  /* query heads                                            */
+  int32_t kv_heads; /* key / value heads (q_heads % kv_heads == 0)            */
+  int32_t n_blocks; /* EncoderBlocks                                          */
+  int32_t seq_len;  /* max_audio_len: the RoPE table has seq_len / 2 rows     */
+} yoho_model_desc;
+
+/* Number and order of the float32 tensors yoho_model_weights_pack consumes:
+ *   0 Conv_0.kernel (3, n_mels, D)  1 Conv_0.bias (D)  2 RMSNorm_0.scale (D)
+ *   3 Conv_1.kernel (3, D, D)       4 Conv_1.bias (D)  5 RMSNorm_1.scale (D)
+ *   6 RoPE table (seq_len / 2, 2, 32): cos | sin of (s + 1) * 10^-i  [RoPE has no params; built by the
+ *     host in the reference's float32 op order, layers.py:31-33]
+ *   then for each EncoderBlock_i, 9 tensors (layers.py:101-109, 65-67, 88, 14-16):
+ *     RMSNorm_0.scale, DenseGeneral_0.kernel (D, q_heads, 64), DenseGeneral_1.kernel (D, kv_heads, 64),
+ *     DenseGeneral_2.kernel (D, kv_heads, 64), Dense_0.kernel (kv_heads*64, D), RMSNorm_1.scale,
+ *     SwiGLU Dense_0.kernel (D, 3D), Dense_1.kernel (D, 3D), Dense_2.kernel (3D, D) */
+int yoho_model_num_tensors(const yoho_model_desc* desc);
+size_t yoho_model_weights_bytes(const yoho_model_desc* desc);
+int yoho_model_weights_pack(yoho_ctx* ctx, const yoho_model_desc* desc, const float* const* tensors,
+                            int n_tensors, void* blob, size_t blob_bytes, yoho_stream_t stream);
+/* frames / 2 (nn.max_pool(x, (1, 2), (1, 2)), model.py:20). */
+int yoho_model_out_len(int frames);
+size_t yoho_model_workspace_bytes(const yoho_model_desc* desc, int batch, int frames, int compute);
+
+/* Replaces state.apply_fn({"params": params}, spectogram, method=Model.encode_audio)
+ * (train/stages/transcription_pretrain_no_voiceprints.py:198-203; model.py:82-83, 16-29).
+ *   mel (batch, frames, n_mels) float32  ->  out (batch, frames / 2, D) float32 */
+int yoho_model_encoder_fwd(yoho_ctx* ctx, const yoho_model_desc* desc, const void* blob, const float* mel,
+                           int batch, int frames, float* out, int compute, void* ws, size_t ws_bytes,
+                           yoho_stream_t stream);
+
 /* ---- measurement hooks (bench.py; not part of the reference surface) ------------------ */
 
 /* Kernels launched by this library in this process so far (the `gpu_launches` evidence). */

@@ -23,6 +23,11 @@ class EncDesc(C.Structure):
                 ("n_layers", C.c_int32), ("seq_len", C.c_int32)]
 
 
+class ModelDesc(C.Structure):
+    _fields_ = [("n_mels", C.c_int32), ("dims", C.c_int32), ("q_heads", C.c_int32), ("kv_heads", C.c_int32),
+                ("n_blocks", C.c_int32), ("seq_len", C.c_int32)]
+
+
 _p, _i, _sz = C.c_void_p, C.c_int, C.c_size_t
 
 # name -> (restype, argtypes); mirrors include/yoho_b200.h one to one
@@ -46,6 +51,12 @@ SIGNATURES = {
     "yoho_encoder_out_len": (_i, [_i]),
     "yoho_encoder_workspace_bytes": (_sz, [C.POINTER(EncDesc), _i, _i, _i]),
     "yoho_encoder_fwd": (_i, [_p, C.POINTER(EncDesc), _p, _p, _i, _i, _p, _i, _p, _sz, _p]),
+    "yoho_model_num_tensors": (_i, [C.POINTER(ModelDesc)]),
+    "yoho_model_weights_bytes": (_sz, [C.POINTER(ModelDesc)]),
+    "yoho_model_weights_pack": (_i, [_p, C.POINTER(ModelDesc), C.POINTER(_p), _i, _p, _sz, _p]),
+    "yoho_model_out_len": (_i, [_i]),
+    "yoho_model_workspace_bytes": (_sz, [C.POINTER(ModelDesc), _i, _i, _i]),
+    "yoho_model_encoder_fwd": (_i, [_p, C.POINTER(ModelDesc), _p, _p, _i, _i, _p, _i, _p, _sz, _p]),
     "yoho_launch_count": (C.c_longlong, []),
     "yoho_prof_enable": (_i, [_i]),
     "yoho_prof_num_classes": (_i, []),

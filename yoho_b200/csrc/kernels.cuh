@@ -16,6 +16,22 @@ int launch_cast_f32(const __nv_bfloat16* src, float* dst, size_t n, cudaStream_t
 int launch_mel_im2col(const float* mel, __nv_bfloat16* dst, int batch, int frames, int frames_padded, int n_mels, int k0, cudaStream_t s);
 int launch_fill_zero(void* p, size_t bytes, cudaStream_t s);
 
+// ---------------------------------------------------------------- yoho_ops.cu (YOHO's own encoder: model.py / layers.py)
+// y = [silu](x * rsqrt(mean(x^2) + 1e-6) * scale), one row at a time
+int launch_rmsnorm_f32(const float* x, const float* scale, float* y, int rows, int dims, int silu, cudaStream_t s);
+int launch_rmsnorm_bf16(const float* x, const float* scale, __nv_bfloat16* y, int rows, int dims, int silu, cudaStream_t s);
+// (batch, in_len, dims) -> (batch, in_len / 2, dims): silu(rmsnorm(x)) then max over time pairs
+int launch_rmsnorm_silu_pool_f32(const float* x, const float* scale, float* y, int batch, int in_len, int dims, cudaStream_t s);
+int launch_rmsnorm_silu_pool_bf16(const float* x, const float* scale, __nv_bfloat16* y, int batch, int in_len, int dims, cudaStream_t s);
+// RoPE in place on the first n_rot_heads 64-wide heads of each row; table (len, 2, 32) float32 {cos, sin}
+int launch_rope_f32(float* qkv, const float* table, long long rows, int seq, int ld, int n_rot_heads, cudaStream_t s);
+int launch_rope_bf16(__nv_bfloat16* qkv, const float* table, long long rows, int seq, int ld, int n_rot_heads, cudaStream_t s);
+// g = silu(h[:, :hidden]) * h[:, hidden:]
+int launch_swiglu_gate_f32(const float* h, float* g, long long rows, int hidden, cudaStream_t s);
+int launch_swiglu_gate_bf16(const __nv_bfloat16* h, __nv_bfloat16* g, long long rows, int hidden, cudaStream_t s);
+// dst (d_in, kv_heads*64; row stride ld_dst) = sum_g src (d_in, kv_heads, groups, 64)
+int launch_group_sum(const float* src, float* dst, int d_in, int kv_heads, int groups, int ld_dst, cudaStream_t s);
+
 // ---------------------------------------------------------------- encoder_fp32.cu (SIMT, 1e-4 path)
 struct SgemmArgs {
   const float* a = nullptr; const float* b = nullptr; float* c = nullptr;

@@ -90,13 +90,16 @@ class Runtime:
         return fb
 
     # ---- encoder weights ------------------------------------------------------------------
-    def packed_weights(self, params: dict, desc: EncDesc, tensors: list):
-        """Pack (once per params object) the float32 tensors into the device blob the kernels read."""
-        key = id(params)
+    def packed_weights(self, params: dict, desc, tensors: list, family: str = "encoder"):
+        """Pack (once per params object) the float32 tensors into the device blob the kernels read.
+        ``family``: "encoder" (yoho_encoder_*: Whisper AudioEncoder) or "model" (yoho_model_*: YOHO's own encoder)."""
+        key = (family, id(params))
         hit = self._weights.get(key)
         if hit is not None and hit[0] is params:
             return hit[1]
-        nbytes = self.lib.yoho_encoder_weights_bytes(C.byref(desc))
+        bytes_fn = getattr(self.lib, f"yoho_{family}_weights_bytes")
+        pack_fn = getattr(self.lib, f"yoho_{family}_weights_pack")
+        nbytes = bytes_fn(C.byref(desc))
         if nbytes == 0:
             raise _lib.YohoError(-1, self.lib.yoho_last_error().decode())
         blob = torch.empty(nbytes + 1024, dtype=torch.uint8, device=self.device)
@@ -110,8 +113,8 @@ class Runtime:
                 ptrs[i] = a.ctypes.data
             keep.append(a)
         with torch.cuda.device(self.device):
-            check(self.lib.yoho_encoder_weights_pack(self.ctx, C.byref(desc), ptrs, len(tensors),
-                                                     C.c_void_p(self.aligned_ptr(blob)), nbytes, self.stream_ptr()))
+            check(pack_fn(self.ctx, C.byref(desc), ptrs, len(tensors), C.c_void_p(self.aligned_ptr(blob)), nbytes,
+                          self.stream_ptr()))
             torch.cuda.current_stream(self.device).synchronize()   # host sources may now be released
         self._weights[key] = (params, blob)
         return blob
