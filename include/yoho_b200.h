@@ -103,6 +103,19 @@ int yoho_logmel_s16(yoho_ctx* ctx, const yoho_filterbank* fb, const int16_t* pcm
                     int n_samples, int n_fft, int hop, float* out, int norm, void* ws,
                     size_t ws_bytes, yoho_stream_t stream);
 
+/* Long-recording ingest (the step before the path: whisper.py:249-253, dataloaders.py:125-128): `recording`
+ * holds total_samples mono samples on the device; clip b is recording[b * clip_samples, (b + 1) * clip_samples),
+ * the last clip zero padded (np.pad, whisper.py:253).  Writes yoho_chunk_count(total_samples, clip_samples) =
+ * ceil(total / clip) rows of (frames, n_mels); size the workspace with yoho_logmel_workspace_bytes(that count, ...).
+ * No intermediate (clips, clip_samples) float32 copy is made: conversion, padding and framing happen in the load. */
+int yoho_chunk_count(long long total_samples, int clip_samples);
+int yoho_logmel_chunked_f32(yoho_ctx* ctx, const yoho_filterbank* fb, const float* recording,
+                            long long total_samples, int clip_samples, int n_fft, int hop, float* out,
+                            int norm, void* ws, size_t ws_bytes, yoho_stream_t stream);
+int yoho_logmel_chunked_s16(yoho_ctx* ctx, const yoho_filterbank* fb, const int16_t* recording,
+                            long long total_samples, int clip_samples, int n_fft, int hop, float* out,
+                            int norm, void* ws, size_t ws_bytes, yoho_stream_t stream);
+
 size_t yoho_normalize_workspace_bytes(int batch, int frames, int n_mels);
 
 /* Stand-alone normalize_spectogram(spectogram) (audio.py:53-58) / Whisper normaliser on an
@@ -158,6 +171,31 @@ size_t yoho_encoder_workspace_bytes(const yoho_enc_desc* desc, int batch, int fr
  * yoho_encoder_out_len(frames) must equal desc->seq_len (whisper.py:23 broadcasts). */
 int yoho_encoder_fwd(yoho_ctx* ctx, const yoho_enc_desc* desc, const void* blob, const float* mel,
                      int batch, int frames, float* out, int compute, void* ws, size_t ws_bytes,
+                     yoho_stream_t stream);
+
+/* ---- cross-attention K/V pre-projection (the step after the path) ------------------------- */
+
+/* Every DecoderBlock applies key_proj / value_proj of its cross MultiHeadAttention to the same encoder states
+ * (whisper.py:104 -> :45-46) and the reference redoes that for every generated token (:274-281; "TODO: add KV
+ * cache", :27).  They depend on the clip only: one data-parallel GEMM per decoder layer, done once here. */
+typedef struct yoho_crosskv_desc {
+  int32_t d_in;     /* encoder width (audio_dims)       */
+  int32_t d_out;    /* decoder width (text_dims)        */
+  int32_t n_layers; /* decoder layers                   */
+} yoho_crosskv_desc;
+
+/* 3 float32 tensors per decoder layer, in order: DecoderBlock_l/MultiHeadAttention_1/key_proj.kernel (d_in, d_out)
+ * [no bias, whisper.py:33], value_proj.kernel (d_in, d_out), value_proj.bias (d_out). */
+int yoho_crosskv_num_tensors(const yoho_crosskv_desc* desc);
+size_t yoho_crosskv_weights_bytes(const yoho_crosskv_desc* desc);
+int yoho_crosskv_weights_pack(yoho_ctx* ctx, const yoho_crosskv_desc* desc, const float* const* tensors,
+                              int n_tensors, void* blob, size_t blob_bytes, yoho_stream_t stream);
+size_t yoho_crosskv_workspace_bytes(const yoho_crosskv_desc* desc, int batch, int t, int compute);
+/* states (batch, t, d_in) float32 -> kv (n_layers, batch, t, 2 * d_out) float32 with [k | v] along the last axis:
+ * k = states @ key_proj.kernel, v = states @ value_proj.kernel + value_proj.bias.  The d_head^-0.25 scaling of k
+ * (whisper.py:54-57) is part of qkv_attention and left to the consumer. */
+int yoho_crosskv_fwd(yoho_ctx* ctx, const yoho_crosskv_desc* desc, const void* blob, const float* states,
+                     int batch, int t, float* kv, int compute, void* ws, size_t ws_bytes,
                      yoho_stream_t stream);
 
 /* ---- YOHO's own audio encoder (next row after the Whisper path) ------------------------ */

@@ -264,3 +264,30 @@ def audio_encoder_torch_cpu(params: dict, mel: np.ndarray, n_heads: int, pos_tab
             x = x + lin(gelu(lin(ln(x, p["LayerNorm_1"]), p["Dense_0"])), p["Dense_1"])
         x = ln(x, params["LayerNorm_0"])
     return x.numpy()
+
+
+# ---------------------------------------------------------------- step after the path
+def cross_attention_kv(text_decoder_params: dict, states: np.ndarray, n_layers: int, dtype=np.float64) -> np.ndarray:
+    """Keys / values the cross attention of every DecoderBlock takes from the encoder states: whisper.py:104 calls
+    ``MultiHeadAttention(q, kv)``, whose ``key_proj`` (no bias, :33) and ``value_proj`` act on ``kv`` (:45-46).
+    Returns (n_layers, B, T, 2 * D_text) with [k | v] along the last axis (unscaled: :54-57 scales inside attention)."""
+    x = np.asarray(states, dtype)
+    out = []
+    for i in range(n_layers):
+        att = text_decoder_params[f"DecoderBlock_{i}"]["MultiHeadAttention_1"]
+        k = x @ np.asarray(att["key_proj"]["kernel"], dtype)
+        v = x @ np.asarray(att["value_proj"]["kernel"], dtype) + np.asarray(att["value_proj"]["bias"], dtype)
+        out.append(np.concatenate([k, v], axis=-1))
+    return np.stack(out)
+
+
+def init_cross_kv_params(d_in: int, d_out: int, n_layers: int, seed: int = 42) -> dict:
+    """Random float32 ``text_decoder`` sub-tree holding only the cross-attention key / value projections."""
+    rng = np.random.default_rng(seed)
+    p = {}
+    for i in range(n_layers):
+        p[f"DecoderBlock_{i}"] = {"MultiHeadAttention_1": {
+            "key_proj": {"kernel": (rng.standard_normal((d_in, d_out)) / math.sqrt(d_in)).astype(np.float32)},
+            "value_proj": {"kernel": (rng.standard_normal((d_in, d_out)) / math.sqrt(d_in)).astype(np.float32),
+                           "bias": (0.1 * rng.standard_normal(d_out)).astype(np.float32)}}}
+    return p

@@ -154,3 +154,23 @@ def test_shape_mismatch_errors(rt):
         AudioEncoder(1500, 128, 2, 1).apply({"params": params}, np.zeros((1, 199, 80), np.float32))
     with pytest.raises(ValueError, match="Conv_0"):
         AudioEncoder(100, 128, 2, 1).apply({"params": params}, np.zeros((1, 199, 128), np.float32))
+
+
+# ------------------------------------------------------------------ cross-attention K/V pre-projection
+@pytest.mark.parametrize("batch,t,d_in,d_out,layers", [(2, 1500, 384, 384, 4), (3, 100, 512, 256, 2), (1, 1500, 768, 768, 1)])
+def test_cross_attention_kv(rt, batch, t, d_in, d_out, layers):
+    from oracle import encoder as eo
+    from yoho_b200.nn import cross_attention_kv
+    params = eo.init_cross_kv_params(d_in, d_out, layers, seed=d_in + t)
+    states = np.random.default_rng(t).standard_normal((batch, t, d_in)).astype(np.float32)
+    want = eo.cross_attention_kv(params, states, layers)
+    got32 = cross_attention_kv(params, states, layers, compute="fp32")
+    assert got32.shape == (layers, batch, t, 2 * d_out)
+    assert np.abs(got32 - want).max() <= TOL_FP32 * max(1.0, float(np.abs(want).max()))
+    got16 = cross_attention_kv(params, states, layers, compute="bf16")
+    assert np.isfinite(got16).all() and _max_rel(got16, want) <= TOL_BF16
+    # key_proj has no bias (whisper.py:33): zero states give k == 0 and v == value_proj.bias exactly
+    zero = cross_attention_kv(params, np.zeros((1, 8, d_in), np.float32), layers, compute="bf16")
+    assert np.array_equal(zero[..., :d_out], np.zeros_like(zero[..., :d_out]))
+    bias = np.stack([params[f"DecoderBlock_{i}"]["MultiHeadAttention_1"]["value_proj"]["bias"] for i in range(layers)])
+    assert np.array_equal(zero[..., d_out:], np.broadcast_to(bias[:, None, None, :], zero[..., d_out:].shape))

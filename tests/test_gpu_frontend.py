@@ -126,3 +126,36 @@ def test_size_independent_properties_at_bench_size(api):
     floor = torch.maximum(peak - 2.0, torch.full_like(peak, -1.5))
     assert ((w.amin(dim=(1, 2)) - floor).abs() < 1e-5).all()
     assert (w >= floor[:, None, None] - 1e-6).all() and (w <= peak[:, None, None]).all()
+
+
+@pytest.mark.parametrize("dtype", [np.int16, np.float32])
+def test_chunked_long_recording_ingest(api, dtype):
+    """one long recording -> ceil(L / clip) clips, last one zero padded (whisper.py:251-253),
+    int16 scaled by 1/32768 on load (whisper.py:249).  Must equal the batched call on the explicitly padded
+    array bit for bit (same kernel arithmetic) and the float64 oracle within 1e-4."""
+    from oracle import frontend as fo
+    rng = np.random.default_rng(7)
+    clip, total = 48000, 48000 * 2 + 17001          # 2 full clips + a ragged tail
+    if dtype == np.int16:
+        rec = (rng.standard_normal(total) * 3000).astype(np.int16)
+        as_float = rec.astype(np.float32) / np.float32(32768.0)
+    else:
+        rec = (0.1 * rng.standard_normal(total)).astype(np.float32)
+        as_float = rec
+    padded = np.zeros(3 * clip, np.float32)
+    padded[:total] = as_float
+    for norm in ("none", "reference", "whisper"):
+        got = api.log_mel_spectogram_chunked(rec, clip_samples=clip, norm=norm)
+        assert got.shape == (3, 299, 80)
+        same = api.log_mel_spectogram(padded.reshape(3, clip), norm=norm)
+        assert np.array_equal(got, same), norm
+    want = fo.log_mel(padded.reshape(3, clip).astype(np.float64), norm_mode=1)
+    assert np.abs(api.log_mel_spectogram_chunked(rec, clip_samples=clip) - want).max() <= TOL
+    # exact multiple and shorter-than-one-clip recordings
+    assert api.log_mel_spectogram_chunked(rec[: 2 * clip], clip_samples=clip).shape[0] == 2
+    short = api.log_mel_spectogram_chunked(rec[:1000], clip_samples=clip, norm="none")
+    assert short.shape == (1, 299, 80) and np.array_equal(short[0, 8:], np.zeros_like(short[0, 8:]))
+    # frame 7 is all padding but shares a packed complex FFT with frame 6: float32 leakage ~ (1e-7)^2 of its power
+    assert short[0, 7].max() <= 1e-12 * short[0, 6].max()
+    with pytest.raises(ValueError):
+        api.log_mel_spectogram_chunked(rec.reshape(1, -1), clip_samples=clip)

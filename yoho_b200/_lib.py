@@ -28,6 +28,10 @@ class ModelDesc(C.Structure):
                 ("n_blocks", C.c_int32), ("seq_len", C.c_int32)]
 
 
+class CrossKvDesc(C.Structure):
+    _fields_ = [("d_in", C.c_int32), ("d_out", C.c_int32), ("n_layers", C.c_int32)]
+
+
 _p, _i, _sz = C.c_void_p, C.c_int, C.c_size_t
 
 # name -> (restype, argtypes); mirrors include/yoho_b200.h one to one
@@ -43,6 +47,9 @@ SIGNATURES = {
     "yoho_logmel_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "yoho_logmel_f32": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _sz, _p]),
     "yoho_logmel_s16": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _sz, _p]),
+    "yoho_chunk_count": (_i, [C.c_longlong, _i]),
+    "yoho_logmel_chunked_f32": (_i, [_p, _p, _p, C.c_longlong, _i, _i, _i, _p, _i, _p, _sz, _p]),
+    "yoho_logmel_chunked_s16": (_i, [_p, _p, _p, C.c_longlong, _i, _i, _i, _p, _i, _p, _sz, _p]),
     "yoho_normalize_workspace_bytes": (_sz, [_i, _i, _i]),
     "yoho_normalize_f32": (_i, [_p, _p, _i, _i, _i, _p, _i, _p, _sz, _p]),
     "yoho_encoder_num_tensors": (_i, [C.POINTER(EncDesc)]),
@@ -51,6 +58,11 @@ SIGNATURES = {
     "yoho_encoder_out_len": (_i, [_i]),
     "yoho_encoder_workspace_bytes": (_sz, [C.POINTER(EncDesc), _i, _i, _i]),
     "yoho_encoder_fwd": (_i, [_p, C.POINTER(EncDesc), _p, _p, _i, _i, _p, _i, _p, _sz, _p]),
+    "yoho_crosskv_num_tensors": (_i, [C.POINTER(CrossKvDesc)]),
+    "yoho_crosskv_weights_bytes": (_sz, [C.POINTER(CrossKvDesc)]),
+    "yoho_crosskv_weights_pack": (_i, [_p, C.POINTER(CrossKvDesc), C.POINTER(_p), _i, _p, _sz, _p]),
+    "yoho_crosskv_workspace_bytes": (_sz, [C.POINTER(CrossKvDesc), _i, _i, _i]),
+    "yoho_crosskv_fwd": (_i, [_p, C.POINTER(CrossKvDesc), _p, _p, _i, _i, _p, _i, _p, _sz, _p]),
     "yoho_model_num_tensors": (_i, [C.POINTER(ModelDesc)]),
     "yoho_model_weights_bytes": (_sz, [C.POINTER(ModelDesc)]),
     "yoho_model_weights_pack": (_i, [_p, C.POINTER(ModelDesc), C.POINTER(_p), _i, _p, _sz, _p]),

@@ -132,7 +132,7 @@ __device__ __forceinline__ void stage_pcm(float* dst, const T* __restrict__ clip
 // norm: 0 mel power, 1 log10(max(x,1e-13)) + {sum,sumsq} partials, 2 log10(max(x,1e-10)) + {max} partials
 template <typename T>
 __global__ void __launch_bounds__(kThreads, 2)
-logmel_kernel(const T* __restrict__ pcm, int n_samples, int n_frames, int clip0,
+logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples, int n_frames, int clip0,
               const float* __restrict__ window, const float2* __restrict__ twiddle,
               const int* __restrict__ fb_lo, const int* __restrict__ fb_len,
               const float* __restrict__ fb_w, int band_stride, int n_mels, float* __restrict__ out,
@@ -146,7 +146,10 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, int n_frames, int clip0,
   const int fft = tid / 20;   // which pair of frames
   const int lane20 = tid % 20;
 
-  stage_pcm<T>(sm.pcm, pcm + size_t(clip) * n_samples, tile * kFramesPerCta * kHop, n_samples, vec_ok != 0);
+  // samples of this clip that exist in `pcm` (a long recording's last clip is short: zero padded, whisper.py:253)
+  const long long left = total_samples - (long long)clip * n_samples;
+  const int valid = left >= n_samples ? n_samples : (left > 0 ? int(left) : 0);
+  stage_pcm<T>(sm.pcm, pcm + size_t(clip) * n_samples, tile * kFramesPerCta * kHop, valid, vec_ok != 0);
   __syncthreads();
 
   float2 v[20];
@@ -367,7 +370,7 @@ static int clips_per_chunk(int frames, int n_mels) {
 }
 
 template <typename T>
-static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm, int batch, int n_samples,
+static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm, int batch, int n_samples, long long total_samples,
                          int n_fft, int hop, float* out, int norm, void* ws, size_t ws_bytes,
                          cudaStream_t stream) {
   if (!ctx || !fb || !pcm || !out) return fail(YOHO_ERR_INVALID, "yoho_logmel: null argument");
@@ -397,7 +400,7 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
     {
       ProfScope prof(stream, kProfFrontend, double(nb) * (double(n_samples) * sizeof(T) + double(elems) * sizeof(float)));
       logmel_kernel<T><<<dim3(tiles, nb), kThreads, sizeof(FrontendSmem), stream>>>(
-          pcm, n_samples, frames, c0, ctx->d_window, ctx->d_twiddle, fb->d_lo, fb->d_len, fb->d_weights,
+          pcm, n_samples, total_samples, frames, c0, ctx->d_window, ctx->d_twiddle, fb->d_lo, fb->d_len, fb->d_weights,
           fb->band_stride, fb->n_mels, out, stats, tiles, norm, vec_ok);
       YOHO_LAUNCH_CHECK("logmel_kernel");
     }
@@ -431,15 +434,44 @@ extern "C" size_t yoho_logmel_workspace_bytes(int batch, int n_samples, int n_ff
 extern "C" int yoho_logmel_f32(yoho_ctx* ctx, const yoho_filterbank* fb, const float* pcm, int batch,
                                int n_samples, int n_fft, int hop, float* out, int norm, void* ws,
                                size_t ws_bytes, yoho_stream_t stream) {
-  return logmel_launch<float>(ctx, fb, pcm, batch, n_samples, n_fft, hop, out, norm, ws, ws_bytes,
+  return logmel_launch<float>(ctx, fb, pcm, batch, n_samples, (long long)batch * n_samples, n_fft, hop, out, norm, ws, ws_bytes,
                               static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int yoho_logmel_s16(yoho_ctx* ctx, const yoho_filterbank* fb, const int16_t* pcm, int batch,
                                int n_samples, int n_fft, int hop, float* out, int norm, void* ws,
                                size_t ws_bytes, yoho_stream_t stream) {
-  return logmel_launch<int16_t>(ctx, fb, pcm, batch, n_samples, n_fft, hop, out, norm, ws, ws_bytes,
+  return logmel_launch<int16_t>(ctx, fb, pcm, batch, n_samples, (long long)batch * n_samples, n_fft, hop, out, norm, ws, ws_bytes,
                                 static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int yoho_chunk_count(long long total_samples, int clip_samples) {
+  if (total_samples < 0 || clip_samples <= 0) return fail(YOHO_ERR_INVALID, "yoho_chunk_count: total=%lld clip=%d", total_samples, clip_samples);
+  long long n = (total_samples + clip_samples - 1) / clip_samples;
+  if (n > 0x7fffffffLL) return fail(YOHO_ERR_UNSUPPORTED, "yoho_chunk_count: %lld clips", n);
+  return int(n);
+}
+
+template <typename T>
+static int logmel_chunked(yoho_ctx* ctx, const yoho_filterbank* fb, const T* recording, long long total_samples, int clip_samples,
+                          int n_fft, int hop, float* out, int norm, void* ws, size_t ws_bytes, yoho_stream_t stream) {
+  if (total_samples < 0) return fail(YOHO_ERR_INVALID, "yoho_logmel_chunked: total_samples=%lld", total_samples);
+  int clips = yoho_chunk_count(total_samples, clip_samples);
+  if (clips < 0) return clips;
+  return logmel_launch<T>(ctx, fb, recording, clips, clip_samples, total_samples, n_fft, hop, out, norm, ws, ws_bytes,
+                          static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int yoho_logmel_chunked_f32(yoho_ctx* ctx, const yoho_filterbank* fb, const float* recording, long long total_samples,
+                                       int clip_samples, int n_fft, int hop, float* out, int norm, void* ws, size_t ws_bytes,
+                                       yoho_stream_t stream) {
+  return logmel_chunked<float>(ctx, fb, recording, total_samples, clip_samples, n_fft, hop, out, norm, ws, ws_bytes, stream);
+}
+
+extern "C" int yoho_logmel_chunked_s16(yoho_ctx* ctx, const yoho_filterbank* fb, const int16_t* recording, long long total_samples,
+                                       int clip_samples, int n_fft, int hop, float* out, int norm, void* ws, size_t ws_bytes,
+                                       yoho_stream_t stream) {
+  return logmel_chunked<int16_t>(ctx, fb, recording, total_samples, clip_samples, n_fft, hop, out, norm, ws, ws_bytes, stream);
 }
 
 extern "C" size_t yoho_normalize_workspace_bytes(int batch, int frames, int n_mels) {

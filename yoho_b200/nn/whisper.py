@@ -19,7 +19,7 @@ from dataclasses import dataclass
 import numpy as np
 import torch
 
-from .._lib import COMPUTE_BF16, COMPUTE_FP32, EncDesc, check
+from .._lib import COMPUTE_BF16, COMPUTE_FP32, CrossKvDesc, EncDesc, check
 from ..runtime import get_runtime
 
 _COMPUTE = {"bf16": COMPUTE_BF16, "fp32": COMPUTE_FP32, COMPUTE_BF16: COMPUTE_BF16, COMPUTE_FP32: COMPUTE_FP32}
@@ -188,3 +188,41 @@ class Whisper:
         params = variables["params"] if "params" in variables else variables
         params = params["audio_encoder"] if "audio_encoder" in params else params
         return self.encode_audio(*args, _params=params, compute=compute, out=out)
+
+
+def flatten_cross_kv_params(text_decoder_params: dict, n_layers: int) -> list:
+    """``DecoderBlock_l/MultiHeadAttention_1/{key_proj.kernel, value_proj.kernel, value_proj.bias}`` in the order
+    ``yoho_crosskv_weights_pack`` expects (MultiHeadAttention_1 is the cross attention, whisper.py:104)."""
+    out = []
+    for i in range(n_layers):
+        att = _leaf(text_decoder_params, f"DecoderBlock_{i}", "MultiHeadAttention_1")
+        out += [_leaf(att, "key_proj", "kernel"), _leaf(att, "value_proj", "kernel"), _leaf(att, "value_proj", "bias")]
+    return out
+
+
+def cross_attention_kv(text_decoder_params: dict, encoded_audio, n_layers: int, compute="bf16", out: torch.Tensor | None = None):
+    """Keys and values every decoder layer's cross attention takes from the encoder states (whisper.py:104 ->
+    :45-46), computed once per clip instead of once per generated token (the reference's ``decode_text`` loop,
+    :274-281).  ``encoded_audio (B, T, D_audio) -> (n_layers, B, T, 2 * D_text)`` float32 with ``[k | v]`` along the
+    last axis; the ``d_head ** -0.25`` scaling of ``k`` stays in the consumer's ``qkv_attention``."""
+    if getattr(encoded_audio, "ndim", None) != 3:
+        raise ValueError("encoded_audio must be (batch, positions, dims)")
+    host = not (isinstance(encoded_audio, torch.Tensor) and encoded_audio.is_cuda)
+    rt = get_runtime(None if host else encoded_audio.device.index)
+    x = rt.to_device(encoded_audio, "states", torch.float32)
+    B, T, D = x.shape
+    tensors = flatten_cross_kv_params(text_decoder_params, n_layers)
+    kshape = tuple(np.shape(tensors[0])) if tensors else (D, D)
+    if kshape[0] != D:
+        raise ValueError(f"key_proj kernel {kshape} does not take {D}-wide encoder states")
+    desc = CrossKvDesc(D, kshape[1], n_layers)
+    blob = rt.packed_weights(text_decoder_params, desc, tensors, family="crosskv")
+    mode = _COMPUTE[compute]
+    if out is None:
+        out = torch.empty((n_layers, B, T, 2 * kshape[1]), dtype=torch.float32, device=rt.device)
+    ws_bytes = rt.lib.yoho_crosskv_workspace_bytes(C.byref(desc), B, T, mode)
+    ws = rt.workspace("crosskv", ws_bytes)
+    with torch.cuda.device(rt.device):
+        check(rt.lib.yoho_crosskv_fwd(rt.ctx, C.byref(desc), C.c_void_p(rt.aligned_ptr(blob)), C.c_void_p(x.data_ptr()), B, T,
+                                      C.c_void_p(out.data_ptr()), mode, C.c_void_p(rt.aligned_ptr(ws)), ws_bytes, rt.stream_ptr()))
+    return out.cpu().numpy() if host else out

@@ -117,3 +117,31 @@ def log_mel_spectogram(audio, n_fft: int = 400, hop_len: int = 160, sample_rate:
     transcription_pretrain_no_voiceprints.py:172-179 and whisper.py:255-256) in one kernel pass;
     ``norm`` is ``"reference"``, ``"whisper"`` or ``"none"``.  Accepts float32 or int16 PCM."""
     return _logmel(audio, n_fft, hop_len, sample_rate, n_mels, _NORMS[norm], out)
+
+
+def log_mel_spectogram_chunked(recording, clip_samples: int = 480000, n_fft: int = 400, hop_len: int = 160, sample_rate: int = 16000,
+                               n_mels: int = 80, norm="reference", out: torch.Tensor | None = None):
+    """Long-recording ingest: one mono recording ``(L,)`` (int16 as ``load_audio`` returns it, audio.py:11-18, or
+    float32) is cut into ``ceil(L / clip_samples)`` clips, the last one zero padded (whisper.py:251-253), and each
+    clip goes through the fused log-mel kernel -- the int16 -> float conversion (``/ 32768``, whisper.py:249), the
+    padding and the framing all happen in the kernel's load, no ``(clips, clip_samples)`` array is materialised.
+    Returns ``(clips, frames, n_mels)`` float32."""
+    if getattr(recording, "ndim", None) != 1:
+        raise ValueError(f"recording must be (samples,); got ndim={getattr(recording, 'ndim', None)}")
+    host = _is_host(recording)
+    rt = _runtime_for(recording)
+    int16 = (recording.dtype == torch.int16) if isinstance(recording, torch.Tensor) else (np.asarray(recording).dtype == np.int16)
+    pcm = rt.to_device(recording, "pcm", torch.int16 if int16 else torch.float32)
+    total = int(pcm.shape[0])
+    clips = check(rt.lib.yoho_chunk_count(total, clip_samples))
+    frames = check(rt.lib.yoho_stft_frames(clip_samples, n_fft, hop_len))
+    fb = rt.filterbank(mel_filter_banks(sample_rate, n_fft, n_mels))
+    if out is None:
+        out = torch.empty((clips, frames, n_mels), dtype=torch.float32, device=rt.device)
+    ws_bytes = rt.lib.yoho_logmel_workspace_bytes(max(clips, 1), clip_samples, n_fft, hop_len, n_mels)
+    ws = rt.workspace("logmel", ws_bytes)
+    fn = rt.lib.yoho_logmel_chunked_s16 if int16 else rt.lib.yoho_logmel_chunked_f32
+    with torch.cuda.device(rt.device):
+        check(fn(rt.ctx, fb, C.c_void_p(pcm.data_ptr()), total, clip_samples, n_fft, hop_len, C.c_void_p(out.data_ptr()),
+                 _NORMS[norm], C.c_void_p(rt.aligned_ptr(ws)), ws_bytes, rt.stream_ptr()))
+    return _finish(out, host)
