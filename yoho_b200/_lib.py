@@ -5,7 +5,10 @@ from __future__ import annotations
 import ctypes as C
 from pathlib import Path
 
-LIB_PATH = Path(__file__).resolve().parent / "lib" / "libyoho_b200.so"
+import os
+
+# YOHO_B200_LIB selects another build of the same library (A/B timing of kernel variants); default: the in-tree build
+LIB_PATH = Path(os.environ.get("YOHO_B200_LIB") or (Path(__file__).resolve().parent / "lib" / "libyoho_b200.so"))
 
 YOHO_OK = 0
 NORM_NONE, NORM_REFERENCE, NORM_WHISPER = 0, 1, 2

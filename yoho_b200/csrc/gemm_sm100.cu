@@ -16,8 +16,8 @@
 // M256 x N(BN) x K16 MMAs that read both CTAs' shared memory and write 128 accumulator rows into each
 // CTA's TMEM.  This halves the B traffic out of L2 per FLOP compared with two independent 128-row CTAs.
 //
-// CTA = 256 threads: warp 0 TMA producer, warp 1 MMA issuer (leader only), warp 2 TMEM allocator,
-// warps 4-7 epilogue (warp w owns TMEM lanes 32*(w%4)..+31).  The epilogue goes TMEM -> registers ->
+// CTA = 384 threads: warp 0 TMA producer, warp 1 MMA issuer (leader only), warp 2 TMEM allocator,
+// warps 4-11 epilogue (warp w owns TMEM lanes 32*(w%4)..+31; the two warps of a quadrant alternate column chunks).  The epilogue goes TMEM -> registers ->
 // (bias / GELU / +pos / mask) -> 128B-swizzled shared staging -> TMA store; the residual add is a TMA
 // reduce-add into the fp32 residual stream (performed in L2, the stream is never read by the SM).
 // 2 TMEM accumulator stages overlap the epilogue of tile i with the MMAs of tile i+1.
@@ -31,8 +31,8 @@ using namespace ptx;
 constexpr int kBlockM = 128;       // accumulator rows per CTA
 constexpr int kPairM = 2 * kBlockM;  // rows per cluster tile
 constexpr int kBlockK = 64;        // 64 bf16 = 128 B = one swizzle row
-constexpr int kGemmThreads = 256;
-constexpr int kEpiWarps = 4;
+constexpr int kGemmThreads = 384;
+constexpr int kEpiWarps = 8;        // two per TMEM lane quadrant: each takes every other column chunk of its 32 rows
 constexpr int kStageBufBytes = 32 * 128;   // one staging buffer: 32 rows x 128 B
 
 struct GemmParams {
@@ -53,8 +53,8 @@ template <int BN> struct GemmCfg {
   static constexpr int kABytes = kBlockM * kBlockK * 2;          // 16 KB
   static constexpr int kBBytes = (BN / 2) * kBlockK * 2;         // this CTA's half of the B tile
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = BN == 256 ? 6 : 8;
-  static constexpr int kStagingBytes = kEpiWarps * 2 * kStageBufBytes;   // 32 KB
+  static constexpr int kStages = BN == 256 ? 5 : 6;
+  static constexpr int kStagingBytes = kEpiWarps * 2 * kStageBufBytes;   // 64 KB
   static constexpr int kTmemCols = 2 * BN;
   static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
   static_assert(kSmemBytes <= 232448, "exceeds the 227 KB dynamic shared memory limit");
@@ -197,8 +197,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
   } else if (warp >= 4) {
     // ===================== epilogue: TMEM -> registers -> swizzled smem -> TMA store / reduce-add =====================
-    const int q = warp - 4;  // == warp % 4: the TMEM lane quadrant this warp may read
-    unsigned char* my_stage = staging + q * 2 * kStageBufBytes;
+    const int q = warp & 3;          // the TMEM lane quadrant this warp may read
+    const int half = (warp - 4) >> 2;  // which of the two warps of the quadrant: takes column chunks half, half + 2, ...
+    unsigned char* my_stage = staging + (warp - 4) * 2 * kStageBufBytes;
     const int sw = lane & 7;
     int buf = 0;
     int it = 0;
@@ -218,7 +219,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (p.out_is_f32) {
           // 32 fp32 columns (= 128 B rows) per staging buffer
 #pragma unroll 1
-          for (int c = 0; c < BN / 32; ++c) {
+          for (int c = half; c < BN / 32; c += 2) {
             const int col0 = nb * BN + c * 32;
             if (col0 >= p.n) break;  // warp-uniform
             uint32_t acc[32];
@@ -246,7 +247,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         } else {
           // 64 bf16 columns (= 128 B rows) per staging buffer
 #pragma unroll 1
-          for (int c = 0; c < BN / 64; ++c) {
+          for (int c = half; c < BN / 64; c += 2) {
             const int col0 = nb * BN + c * 64;
             if (col0 >= p.n) break;  // warp-uniform
             uint32_t acc0[32], acc1[32];
