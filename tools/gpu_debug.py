@@ -180,6 +180,27 @@ def stage_perf():
         print(f"[perf] encoder {name} B={b} bf16: {ms:.2f} ms  {b * gf / ms:.1f} TFLOP/s  {b * 30 / ms * 1000:.0f}x realtime")
 
 
+def stage_yohoperf():
+    """YOHO's own config (train/config.toml:7-18): 164080-sample clips -> (B, 1024, 128) log-mel -> own encoder (384/6/3/4)."""
+    from yoho_b200 import preprocessing as pp
+    from yoho_b200.nn.model import AudioEncoder, init_yoho_encoder_params
+    B, N = 512, 164080
+    pcm = torch.from_numpy(synth_batch(B, N, unique=8)).cuda()
+    mel = torch.empty((B, 1024, 128), device="cuda")
+    ms_f = timed(lambda: pp.log_mel_spectogram(pcm, n_mels=128, norm="reference", out=mel))
+    params = init_yoho_encoder_params(128, 384, 6, 3, 4, seed=1)
+    enc = AudioEncoder(6, 3, 384, 1024, 4)
+    out = torch.empty((B, 512, 384), device="cuda")
+    ms_e = timed(lambda: enc.apply({"params": params}, mel, compute="bf16", out=out), iters=5, warm=2)
+    # per clip: conv0 2*1024*384*384, conv1 2*512*1152*384, per block qkv 2*512*384*576, attention 4*512^2*192,
+    # out 2*512*192*384, w12 2*512*384*2304, w3 2*512*1152*384
+    gf = (2 * 1024 * 384 * 384 + 2 * 512 * 1152 * 384 + 4 * (2 * 512 * 384 * 576 + 4 * 512 * 512 * 192 + 2 * 512 * 192 * 384
+                                                           + 2 * 512 * 384 * 2304 + 2 * 512 * 1152 * 384)) / 1e9
+    secs = N / 16000.0
+    print(f"[yohoperf] B={B} clips of {secs:.2f} s: log-mel {ms_f:.3f} ms, encoder {ms_e:.2f} ms ({B * gf / ms_e:.1f} TFLOP/s, {gf:.2f} GFLOP/clip), "
+          f"{B * secs / (ms_f + ms_e) * 1000:.0f}x realtime")
+
+
 def stage_gemmperf():
     """Times the tcgen05 GEMM alone on the encoder's shapes (whisper-small, 64 clips = 96000 rows)."""
     rt = get_runtime()
