@@ -180,6 +180,21 @@ def stage_perf():
         print(f"[perf] encoder {name} B={b} bf16: {ms:.2f} ms  {b * gf / ms:.1f} TFLOP/s  {b * 30 / ms * 1000:.0f}x realtime")
 
 
+def stage_logmelperf():
+    """Frontend alone: Whisper shape (80 mels, 30 s) in float32 and int16, YOHO shape (128 mels, 10.26 s)."""
+    from yoho_b200 import preprocessing as pp
+    for B, N, M, F in ((256, 480000, 80, 2999), (512, 164080, 128, 1024)):
+        f32 = torch.from_numpy(synth_batch(B, N, unique=8)).cuda()
+        s16 = (f32 * 32767.0).round().clamp(-32768, 32767).to(torch.int16)
+        out = torch.empty((B, F, M), device="cuda")
+        for name, pcm in (("f32", f32), ("s16", s16)):
+            for norm in ("none", "reference"):
+                ms = timed(lambda: pp.log_mel_spectogram(pcm, n_mels=M, norm=norm, out=out), iters=20, warm=3)
+                gbs = B * (N * pcm.element_size() + F * M * 4) / ms / 1e6
+                print(f"[logmelperf] B={B} N={N} M={M} {name} norm={norm}: {ms:.3f} ms  {gbs:.0f} GB/s algorithmic "
+                      f"({gbs / 6540.2 * 100:.1f}% of measured HBM peak)  {B * N / 16000.0 / ms * 1000:.0f}x realtime")
+
+
 def stage_yohoperf():
     """YOHO's own config (train/config.toml:7-18): 164080-sample clips -> (B, 1024, 128) log-mel -> own encoder (384/6/3/4)."""
     from yoho_b200 import preprocessing as pp

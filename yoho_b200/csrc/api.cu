@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <algorithm>
 #include <vector>
 
 namespace yoho {
@@ -170,35 +171,51 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
   *out = nullptr;
   if (n_mels <= 0 || n_bins <= 0) return fail(YOHO_ERR_INVALID, "yoho_filterbank_create: shape (%d, %d)", n_mels, n_bins);
   YOHO_CUDA_CHECK(cudaSetDevice(ctx->device));
+  if (n_mels > kMelWarps * kMelMaxRounds) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: n_mels=%d > %d", n_mels, kMelWarps * kMelMaxRounds);
+  if (n_bins > kMelPRows) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: n_bins=%d > %d", n_bins, kMelPRows);
   std::vector<int> lo(n_mels, 0), len(n_mels, 0);
-  int max_len = 1;
   for (int m = 0; m < n_mels; ++m) {
     int first = -1, last = -1;
     for (int k = 0; k < n_bins; ++k)
       if (host_filters[size_t(m) * n_bins + k] != 0.0f) { if (first < 0) first = k; last = k; }
     if (first >= 0) { lo[m] = first; len[m] = last - first + 1; }
-    if (len[m] > max_len) max_len = len[m];
   }
-  const int stride = (max_len + 3) / 4 * 4;
+  std::vector<int> order(n_mels);
+  for (int m = 0; m < n_mels; ++m) order[m] = m;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return len[a] > len[b]; });
+  MelSchedule sched = {};
+  sched.rounds = (n_mels + kMelWarps - 1) / kMelWarps;
+  for (int r = 0; r < sched.rounds; ++r) {
+    int n4 = (len[order[r * kMelWarps]] + 3) / 4;      // the round's longest band comes first
+    if (n4 > 255) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: band of %d bins", len[order[r * kMelWarps]]);
+    sched.n4[r] = (unsigned char)n4;
+  }
+  const int stride = 4 * (sched.n4[0] > 0 ? sched.n4[0] : 1);
+  if (size_t(n_mels) * stride > size_t(kMelMaxWeights))
+    return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: %d bands x %d bins exceed the kernel's %d-float weight tile", n_mels, stride, kMelMaxWeights);
   // |2 X[k]|^2 comes out of the packed-pair FFT; stft scales by 1/sum(w) (scaling='spectrum').
   const double scale = 0.25 / (ctx->window_sum * ctx->window_sum);
   std::vector<float> w(size_t(n_mels) * stride, 0.0f);
-  for (int m = 0; m < n_mels; ++m)
+  std::vector<int2> bands(n_mels);
+  for (int r = 0; r < n_mels; ++r) {
+    const int m = order[r], walked = 4 * sched.n4[r / kMelWarps];
+    const int first = lo[m] + walked <= kMelPRows ? lo[m] : kMelPRows - walked;   // keep the walk inside the power tile
+    bands[r] = make_int2(m, first);
     for (int j = 0; j < len[m]; ++j)
-      w[size_t(m) * stride + j] = float(double(host_filters[size_t(m) * n_bins + lo[m] + j]) * scale);
+      w[size_t(r) * stride + (lo[m] - first) + j] = float(double(host_filters[size_t(m) * n_bins + lo[m] + j]) * scale);
+  }
   yoho_filterbank* fb = new (std::nothrow) yoho_filterbank();
   if (!fb) return fail(YOHO_ERR_INVALID, "yoho_filterbank_create: out of host memory");
   fb->device = ctx->device;
   fb->n_mels = n_mels;
   fb->n_bins = n_bins;
   fb->band_stride = stride;
+  fb->sched = sched;
   fb->power_scale = scale;
   cudaError_t e;
-  if ((e = cudaMalloc(&fb->d_lo, n_mels * sizeof(int))) != cudaSuccess ||
-      (e = cudaMalloc(&fb->d_len, n_mels * sizeof(int))) != cudaSuccess ||
+  if ((e = cudaMalloc(&fb->d_bands, n_mels * sizeof(int2))) != cudaSuccess ||
       (e = cudaMalloc(&fb->d_weights, w.size() * sizeof(float))) != cudaSuccess ||
-      (e = cudaMemcpy(fb->d_lo, lo.data(), n_mels * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess ||
-      (e = cudaMemcpy(fb->d_len, len.data(), n_mels * sizeof(int), cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(fb->d_bands, bands.data(), n_mels * sizeof(int2), cudaMemcpyHostToDevice)) != cudaSuccess ||
       (e = cudaMemcpy(fb->d_weights, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess) {
     yoho_filterbank_destroy(fb);
     return fail(YOHO_ERR_CUDA, "yoho_filterbank_create: %s", cudaGetErrorString(e));
@@ -209,8 +226,7 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
 
 extern "C" int yoho_filterbank_destroy(yoho_filterbank* fb) {
   if (!fb) return YOHO_OK;
-  if (fb->d_lo) cudaFree(fb->d_lo);
-  if (fb->d_len) cudaFree(fb->d_len);
+  if (fb->d_bands) cudaFree(fb->d_bands);
   if (fb->d_weights) cudaFree(fb->d_weights);
   delete fb;
   return YOHO_OK;

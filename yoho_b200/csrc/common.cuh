@@ -72,12 +72,19 @@ struct yoho_ctx {
   void* encode_tiled = nullptr; // cuTensorMapEncodeTiled driver entry point
 };
 
+// Mel filterbank as the log-mel kernel consumes it: bands sorted longest first and dealt to the kernel's
+// kMelWarps warps round by round (boustrophedon); every band of a round is walked 4 * round_n4 bins.
+constexpr int kMelWarps = 10;          // warps of logmel_kernel
+constexpr int kMelPRows = 204;         // rows of the kernel's power tile: 201 bins rounded up to the 4-bin step
+constexpr int kMelMaxRounds = 16;      // n_mels <= 160
+constexpr int kMelMaxWeights = 3072;   // floats of band weights held in shared memory
+struct MelSchedule { int rounds; unsigned char n4[kMelMaxRounds]; };
 struct yoho_filterbank {
   int device = -1;
   int n_mels = 0, n_bins = 0;
-  int band_stride = 0;        // floats per row in d_weights
-  int* d_lo = nullptr;        // first bin of each band
-  int* d_len = nullptr;       // band length (0 for an all-zero row)
-  float* d_weights = nullptr; // (n_mels, band_stride), already multiplied by the STFT power scale
+  int band_stride = 0;        // floats per row in d_weights (multiple of 4)
+  MelSchedule sched = {};
+  int2* d_bands = nullptr;    // sorted position -> {mel row, first bin walked}
+  float* d_weights = nullptr; // (n_mels, band_stride) in sorted order, zero padded, already multiplied by the STFT power scale
   double power_scale = 0.0;   // 0.25 / window_sum^2 folded into d_weights
 };

@@ -11,13 +11,19 @@
 //   out   (B, F, M)     float32, time-major / mel-last (what audio.py:36's einsum returns)
 //   stats (B, tiles, 2) float32 per-tile partials {sum, sum of squares} or {max, -}
 //
-// One CTA = 32 consecutive frames of one clip = 16 complex FFTs of length 400, two real frames
+// One tile = 32 consecutive frames of one clip = 16 complex FFTs of length 400, two real frames
 // packed as (re, im).  400 = 20 x 20: each FFT is run by 20 threads, each doing one radix-20
 // butterfly per pass entirely in registers (radix-20 = 4 x 5 by the prime-factor map, so no
-// internal twiddles), with one shared-memory transpose between the passes.  The 5360 PCM
-// samples a tile needs are staged once in shared memory with 128-bit loads (each sample is used
-// by 2.5 frames), the two real spectra are untangled from Z[k], Z[400-k], and the mel bands
-// (<= 2 filters touch any FFT bin) are applied from shared memory.
+// internal twiddles), with one shared-memory transpose between the passes.  The kernel is
+// persistent (two CTAs per SM walk the (clip, tile) list): the 5360 PCM samples of the NEXT tile
+// are fetched with 16-byte cp.async into the second half of a double buffer while the current tile
+// is transformed (each sample is used by 2.5 frames; int16 is converted when it is read).  The two
+// real spectra are untangled from Z[k], Z[400-k] through registers and the power spectrum is
+// written back over Z bin-major, P[k][frame].  The mel bands (<= 2 filters touch any FFT bin) are
+// then applied with lane = frame: a warp takes whole bands (dealt longest-first, boustrophedon,
+// so the ten warps get equal work), the band's weights are warp-uniform 128-bit loads, there is
+// no divergence, and the (32 frames x n_mels) result is transposed through shared memory so the
+// global stores are full 128-byte lines.
 #include "common.cuh"
 
 namespace yoho {
@@ -31,17 +37,24 @@ constexpr int kThreads = kFftsPerCta * 20;                      // 320
 constexpr int kTileSamples = (kFramesPerCta - 1) * kHop + kNfft;  // 5360
 constexpr int kERow = 21;                                       // padded row (float2) of the transpose buffer
 constexpr int kEFft = 20 * kERow;                               // 420 float2 per FFT
-constexpr int kPStride = 201;
-constexpr int kMelFramesPerTask = 8;
-constexpr int kMelGroups = kFramesPerCta / kMelFramesPerTask;   // 4
+constexpr int kZFft = 404;                                      // float2 per FFT of Z: 808 words = 8 mod 32 keeps the 20-thread groups off each other's banks
+constexpr int kPRow = kFramesPerCta + 1;                        // floats per bin row of P[k][frame]: odd, so bin-strided writes spread over the banks
+constexpr int kPRows = kMelPRows;                               // 201 bins, rounded up: bands are walked four bins at a time
+constexpr int kMaxMels = kMelWarps * kMelMaxRounds;             // the output transpose buffer holds 32 x (n_mels | 1) floats
+constexpr int kWarps = kThreads / 32;
+static_assert(kWarps == kMelWarps, "the filterbank's round schedule is built for this many warps");
 
+template <typename T>
 struct FrontendSmem {
-  float pcm[kTileSamples];
-  float2 ez[kFftsPerCta * kEFft];  // pass-1 -> pass-2 transpose; reused for Z in natural order
-  float power[kFramesPerCta * kPStride];
+  T raw[2][kTileSamples];          // double-buffered PCM tile, as it lies in global memory
+  float2 ez[kFftsPerCta * kEFft];  // pass-1 -> pass-2 transpose; then Z in natural order; then the power spectrum
+  float mel_w[kMelMaxWeights];     // band weights, sorted order (resident for the whole kernel)
+  int2 mel_band[kMaxMels];
   float red[2 * 32];
 };
-static_assert(kFftsPerCta * 400 <= kFftsPerCta * kEFft, "Z must fit in the transpose buffer");
+static_assert(kFftsPerCta * kZFft <= kFftsPerCta * kEFft, "Z must fit in the transpose buffer");
+static_assert(kPRows * kPRow + kFramesPerCta * (kMaxMels | 1) <= 2 * kFftsPerCta * kEFft, "P and the output tile overlay the transpose buffer");
+static_assert((kTileSamples * sizeof(int16_t)) % 16 == 0, "second PCM buffer stays 16-byte aligned");
 
 // ---- radix-20 butterfly (prime-factor 4 x 5), forward sign ------------------------------
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
@@ -104,141 +117,202 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+__device__ __forceinline__ float lg2_approx(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 template <typename T> __device__ __forceinline__ float pcm_to_float(T v);
 template <> __device__ __forceinline__ float pcm_to_float<float>(float v) { return v; }
 template <> __device__ __forceinline__ float pcm_to_float<int16_t>(int16_t v) { return float(v) * (1.0f / 32768.0f); }
 
-// Stage the tile's samples [s0, s0 + kTileSamples) of one clip into shared memory, zero past N
-// (the stft tail padding, audio.py:33 `padded=True`).
+__device__ __forceinline__ void cp_async_16_zfill(void* smem_dst, const void* gmem_src, int src_bytes) {
+  uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gmem_src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Start copying samples [s0, s0 + kTileSamples) of one clip into shared memory, zero past `valid`
+// (the stft tail padding, audio.py:33 `padded=True`, and the short last clip of a long recording).
+// vec_ok: clip base and length are 16-byte multiples, so every chunk is one zero-filling cp.async.
 template <typename T>
-__device__ __forceinline__ void stage_pcm(float* dst, const T* __restrict__ clip, int s0, int n_samples,
-                                          bool vec_ok) {
-  constexpr int kVec = 16 / sizeof(T);  // elements per 128-bit load
-  for (int i = threadIdx.x * kVec; i < kTileSamples; i += kThreads * kVec) {
-    int g = s0 + i;
-    if (vec_ok && g + kVec <= n_samples && i + kVec <= kTileSamples) {
-      int4 raw = __ldg(reinterpret_cast<const int4*>(clip + g));
-      const T* e = reinterpret_cast<const T*>(&raw);
+__device__ __forceinline__ void stage_pcm_async(T* dst, const T* __restrict__ pcm, size_t clip_off, int s0, int valid,
+                                                bool vec_ok) {
+  constexpr int kVec = 16 / sizeof(T);  // elements per 128-bit chunk
+  const T* clip = pcm + clip_off;
+  if (vec_ok && s0 + kTileSamples <= valid) {      // interior tile: every chunk is whole
+    const T* src = clip + s0;
 #pragma unroll
-      for (int j = 0; j < kVec; ++j) dst[i + j] = pcm_to_float<T>(e[j]);
-    } else {
-#pragma unroll
-      for (int j = 0; j < kVec; ++j)
-        if (i + j < kTileSamples) dst[i + j] = (g + j < n_samples) ? pcm_to_float<T>(__ldg(clip + g + j)) : 0.0f;
+    for (int i = threadIdx.x * kVec, it = 0; it < (kTileSamples + kThreads * kVec - 1) / (kThreads * kVec); ++it, i += kThreads * kVec)
+      if (i < kTileSamples) cp_async_16_zfill(dst + i, src + i, 16);
+  } else if (vec_ok) {
+    for (int i = threadIdx.x * kVec; i < kTileSamples; i += kThreads * kVec) {
+      int g = s0 + i;
+      int n = valid - g;
+      n = n < 0 ? 0 : (n > kVec ? kVec : n);
+      cp_async_16_zfill(dst + i, n > 0 ? clip + g : pcm, n * int(sizeof(T)));
+    }
+  } else {
+    for (int i = threadIdx.x; i < kTileSamples; i += kThreads) {
+      int g = s0 + i;
+      dst[i] = g < valid ? __ldg(clip + g) : T(0);
     }
   }
 }
 
 // norm: 0 mel power, 1 log10(max(x,1e-13)) + {sum,sumsq} partials, 2 log10(max(x,1e-10)) + {max} partials
+// Work item = clip0 * tiles_per_clip + i, i < n_items: clip = item / tiles_per_clip, tile = item % tiles_per_clip.
 template <typename T>
 __global__ void __launch_bounds__(kThreads, 2)
-logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples, int n_frames, int clip0,
+logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples, int n_frames, int clip0, int n_items,
               const float* __restrict__ window, const float2* __restrict__ twiddle,
-              const int* __restrict__ fb_lo, const int* __restrict__ fb_len,
-              const float* __restrict__ fb_w, int band_stride, int n_mels, float* __restrict__ out,
+              const int2* __restrict__ fb_bands, const float* __restrict__ fb_w, int band_stride, int n_mels,
+              const __grid_constant__ MelSchedule sched, float* __restrict__ out,
               float2* __restrict__ stats, int tiles_per_clip, int norm, int vec_ok) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  FrontendSmem& sm = *reinterpret_cast<FrontendSmem*>(smem_raw);
+  FrontendSmem<T>& sm = *reinterpret_cast<FrontendSmem<T>*>(smem_raw);
 
-  const int tile = blockIdx.x;
-  const int clip = clip0 + blockIdx.y;
   const int tid = threadIdx.x;
   const int fft = tid / 20;   // which pair of frames
   const int lane20 = tid % 20;
-
-  // samples of this clip that exist in `pcm` (a long recording's last clip is short: zero padded, whisper.py:253)
-  const long long left = total_samples - (long long)clip * n_samples;
-  const int valid = left >= n_samples ? n_samples : (left > 0 ? int(left) : 0);
-  stage_pcm<T>(sm.pcm, pcm + size_t(clip) * n_samples, tile * kFramesPerCta * kHop, valid, vec_ok != 0);
-  __syncthreads();
-
-  float2 v[20];
-  // ---- pass 1: this thread owns n2 = lane20; DFT over n1 of x[20 n1 + n2] -----------------
-  {
-    const float* fa = sm.pcm + (2 * fft) * kHop;  // frame A -> real part
-    const float* fb = fa + kHop;                  // frame B -> imaginary part
-#pragma unroll
-    for (int n1 = 0; n1 < 20; ++n1) {
-      int n = 20 * n1 + lane20;
-      float w = __ldg(window + n);
-      v[n1] = make_float2(fa[n] * w, fb[n] * w);
-    }
-    dft20(v);
-    float2* e = sm.ez + fft * kEFft + lane20;  // E[fft][k1][n2]
-#pragma unroll
-    for (int k1 = 0; k1 < 20; ++k1) {
-      float2 tw = __ldg(twiddle + k1 * 20 + lane20);  // W_400^(n2 k1)
-      e[k1 * kERow] = cmul(v[k1], tw);
-    }
-  }
-  __syncthreads();
-  // ---- pass 2: this thread owns k1 = lane20; DFT over n2 -> Z[k1 + 20 k2] ------------------
-  {
-    const float2* e = sm.ez + fft * kEFft + lane20 * kERow;
-#pragma unroll
-    for (int n2 = 0; n2 < 20; ++n2) v[n2] = e[n2];
-    dft20(v);
-  }
-  __syncthreads();  // every thread has read its row before Z overwrites the buffer
-  {
-    float2* z = sm.ez + fft * 400 + lane20;
-#pragma unroll
-    for (int k2 = 0; k2 < 20; ++k2) z[20 * k2] = v[k2];
-  }
-  __syncthreads();
-  // ---- untangle the two real spectra and take |.|^2 (scale folded into the mel weights) ----
-  for (int i = tid; i < kFftsPerCta * kBins; i += kThreads) {
-    int f = i / kBins, k = i - f * kBins;
-    const float2* z = sm.ez + f * 400;
-    float2 a = z[k];
-    float2 b = z[k == 0 ? 0 : 400 - k];
-    float ar = a.x + b.x, ai = a.y - b.y;  // 2 * X_A[k]
-    float br = a.y + b.y, bi = a.x - b.x;  // 2 * X_B[k] (up to a unit factor)
-    sm.power[(2 * f) * kPStride + k] = fmaf(ar, ar, ai * ai);
-    sm.power[(2 * f + 1) * kPStride + k] = fmaf(br, br, bi * bi);
-  }
-  __syncthreads();
-  // ---- banded mel projection, log10, per-tile statistics -----------------------------------
+  const int warp = tid >> 5, lane = tid & 31;
   const float log_floor = (norm == YOHO_NORM_WHISPER) ? 1e-10f : 1e-13f;
-  float acc_sum = 0.0f, acc_sq = 0.0f, acc_max = -INFINITY;
-  const int frame0 = tile * kFramesPerCta;
-  float* out_clip = out + size_t(clip) * n_frames * n_mels;
-  for (int task = tid; task < n_mels * kMelGroups; task += kThreads) {
-    int g = task / n_mels, m = task - g * n_mels;
-    int lo = __ldg(fb_lo + m), len = __ldg(fb_len + m);
-    const float* wrow = fb_w + size_t(m) * band_stride;
-    const float* p = sm.power + (g * kMelFramesPerTask) * kPStride + lo;
-    float acc[kMelFramesPerTask];
+  const int o_stride = n_mels | 1;
+
+  auto stage = [&](int item, int buf) {
+    int clip = clip0 + item / tiles_per_clip, tile = item % tiles_per_clip;
+    // samples of this clip that exist in `pcm` (a long recording's last clip is short: zero padded, whisper.py:253)
+    const long long left = total_samples - (long long)clip * n_samples;
+    const int valid = left >= n_samples ? n_samples : (left > 0 ? int(left) : 0);
+    stage_pcm_async<T>(sm.raw[buf], pcm, size_t(clip) * n_samples, tile * kFramesPerCta * kHop, valid, vec_ok != 0);
+  };
+
+  int item = blockIdx.x;
+  if (item >= n_items) return;
+  float win[20];
 #pragma unroll
-    for (int q = 0; q < kMelFramesPerTask; ++q) acc[q] = 0.0f;
-    for (int j = 0; j < len; ++j) {
-      float w = __ldg(wrow + j);
+  for (int n1 = 0; n1 < 20; ++n1) win[n1] = __ldg(window + 20 * n1 + lane20);
+  stage(item, 0);
+  cp_async_commit();
+  for (int i = tid; i < n_mels * band_stride; i += kThreads) sm.mel_w[i] = __ldg(fb_w + i);
+  for (int i = tid; i < n_mels; i += kThreads) sm.mel_band[i] = __ldg(fb_bands + i);
+
+  for (int buf = 0; item < n_items; item += gridDim.x, buf ^= 1) {
+    const int clip = clip0 + item / tiles_per_clip, tile = item % tiles_per_clip;
+    cp_async_wait_all();
+    __syncthreads();  // this tile's samples have landed; the previous tile's power rows and red[] are free
+    if (item + int(gridDim.x) < n_items) stage(item + gridDim.x, buf ^ 1);
+    cp_async_commit();
+
+    float2 v[20];
+    // ---- pass 1: this thread owns n2 = lane20; DFT over n1 of x[20 n1 + n2] -----------------
+    {
+      const T* fa = sm.raw[buf] + (2 * fft) * kHop + lane20;  // frame A -> real part
+      const T* fb = fa + kHop;                                // frame B -> imaginary part
 #pragma unroll
-      for (int q = 0; q < kMelFramesPerTask; ++q) acc[q] = fmaf(w, p[q * kPStride + j], acc[q]);
-    }
+      for (int n1 = 0; n1 < 20; ++n1)
+        v[n1] = make_float2(pcm_to_float<T>(fa[20 * n1]) * win[n1], pcm_to_float<T>(fb[20 * n1]) * win[n1]);
+      dft20(v);
+      float2* e = sm.ez + fft * kEFft + lane20;  // E[fft][k1][n2]
 #pragma unroll
-    for (int q = 0; q < kMelFramesPerTask; ++q) {
-      int frame = frame0 + g * kMelFramesPerTask + q;
-      if (frame < n_frames) {
-        float val = acc[q];
-        if (norm != YOHO_NORM_NONE) {
-          val = __log2f(fmaxf(val, log_floor)) * 0.30102999566398120f;
-          acc_sum += val;
-          acc_sq = fmaf(val, val, acc_sq);
-          acc_max = fmaxf(acc_max, val);
-        }
-        out_clip[size_t(frame) * n_mels + m] = val;
+      for (int k1 = 0; k1 < 20; ++k1) {
+        float2 tw = __ldg(twiddle + k1 * 20 + lane20);  // W_400^(n2 k1)
+        e[k1 * kERow] = cmul(v[k1], tw);
       }
     }
-  }
-  if (norm != YOHO_NORM_NONE) {
-    const int warp = tid >> 5, lane = tid & 31;
-    float a = (norm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sum) : warp_max(acc_max);
-    float b = (norm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sq) : 0.0f;
-    if (lane == 0) { sm.red[warp] = a; sm.red[32 + warp] = b; }
     __syncthreads();
-    if (warp == 0) {
-      constexpr int kWarps = kThreads / 32;
+    // ---- pass 2: this thread owns k1 = lane20; DFT over n2 -> Z[k1 + 20 k2] ------------------
+    {
+      const float2* e = sm.ez + fft * kEFft + lane20 * kERow;
+#pragma unroll
+      for (int n2 = 0; n2 < 20; ++n2) v[n2] = e[n2];
+      dft20(v);
+    }
+    __syncthreads();  // every thread has read its row before Z overwrites the buffer
+    {
+      float2* z = sm.ez + fft * kZFft + lane20;
+#pragma unroll
+      for (int k2 = 0; k2 < 20; ++k2) z[20 * k2] = v[k2];
+    }
+    __syncthreads();
+    // ---- untangle the two real spectra and take |.|^2 (scale folded into the mel weights) ----
+    // bins k = lane20 + 20 j of this thread's own FFT, through registers: the power rows of frames
+    // 2 fft and 2 fft + 1 replace Z of the same FFT.
+    {
+      const float2* z = sm.ez + fft * kZFft;
+      float pa[11], pb[11];
+#pragma unroll
+      for (int j = 0; j < 11; ++j) {
+        int k = lane20 + 20 * j;
+        if (j < 10 || lane20 == 0) {
+          float2 a = z[k];
+          float2 b = z[k == 0 ? 0 : 400 - k];
+          float ar = a.x + b.x, ai = a.y - b.y;  // 2 * X_A[k]
+          float br = a.y + b.y, bi = a.x - b.x;  // 2 * X_B[k] (up to a unit factor)
+          pa[j] = fmaf(ar, ar, ai * ai);
+          pb[j] = fmaf(br, br, bi * bi);
+        }
+      }
+      __syncthreads();
+      float* p = reinterpret_cast<float*>(sm.ez) + lane20 * kPRow + 2 * fft;   // P[k][frame]
+#pragma unroll
+      for (int j = 0; j < 11; ++j)
+        if (j < 10 || lane20 == 0) { p[20 * j * kPRow] = pa[j]; p[20 * j * kPRow + 1] = pb[j]; }
+    }
+    __syncthreads();
+    // ---- banded mel projection (lane = frame), log10, per-tile statistics ----------------------
+    // rows 201..203 of P are whatever Z left there (finite); the weights beyond a band are zero.
+    float acc_sum = 0.0f, acc_sq = 0.0f, acc_max = -INFINITY;
+    const int frame0 = tile * kFramesPerCta;
+    const float* power = reinterpret_cast<const float*>(sm.ez);
+    float* otile = reinterpret_cast<float*>(sm.ez) + kPRows * kPRow;          // [frame][o_stride]
+    const bool lane_valid = frame0 + lane < n_frames;
+    for (int round = 0; round < sched.rounds; ++round) {
+      const int r = round * kWarps + ((round & 1) ? kWarps - 1 - warp : warp);
+      const int n4 = sched.n4[round];                                         // the same for every warp: a uniform loop
+      if (r < n_mels) {
+        const int2 band = sm.mel_band[r];                                     // {mel row, first bin}
+        const float* pk = power + band.y * kPRow + lane;
+        const float4* w4 = reinterpret_cast<const float4*>(sm.mel_w + r * band_stride);
+        float a0 = 0.0f, a1 = 0.0f;
+#pragma unroll 1
+        for (int i = 0; i < n4; ++i) {
+          const float4 w = w4[i];
+          a0 = fmaf(w.x, pk[0], a0);
+          a1 = fmaf(w.y, pk[kPRow], a1);
+          a0 = fmaf(w.z, pk[2 * kPRow], a0);
+          a1 = fmaf(w.w, pk[3 * kPRow], a1);
+          pk += 4 * kPRow;
+        }
+        float val = a0 + a1;
+        if (norm != YOHO_NORM_NONE) {
+          val = lg2_approx(fmaxf(val, log_floor)) * 0.30102999566398120f;     // the floor keeps the argument normal
+          if (lane_valid) {
+            acc_sum += val;
+            acc_sq = fmaf(val, val, acc_sq);
+            acc_max = fmaxf(acc_max, val);
+          }
+        }
+        otile[lane * o_stride + band.x] = val;
+      }
+    }
+    if (norm != YOHO_NORM_NONE) {
+      float a = (norm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sum) : warp_max(acc_max);
+      float b = (norm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sq) : 0.0f;
+      if (lane == 0) { sm.red[warp] = a; sm.red[32 + warp] = b; }
+    }
+    __syncthreads();
+    // ---- the tile's (frames, n_mels) block is contiguous in `out`: full-line stores ----------------
+    {
+      float* out_tile = out + (size_t(clip) * n_frames + frame0) * n_mels;
+      const int rows = min(kFramesPerCta, n_frames - frame0);
+      for (int f = warp; f < rows; f += kWarps)
+        for (int m = lane; m < n_mels; m += 32) out_tile[f * n_mels + m] = otile[f * o_stride + m];
+    }
+    if (norm != YOHO_NORM_NONE && warp == 0) {
+      float a, b;
       if (norm == YOHO_NORM_REFERENCE) {
         a = warp_sum(lane < kWarps ? sm.red[lane] : 0.0f);
         b = warp_sum(lane < kWarps ? sm.red[32 + lane] : 0.0f);
@@ -379,6 +453,7 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
   if (norm < YOHO_NORM_NONE || norm > YOHO_NORM_WHISPER) return fail(YOHO_ERR_INVALID, "yoho_logmel: norm=%d", norm);
   if (n_fft != kNfft || hop != kHop)
     return fail(YOHO_ERR_UNSUPPORTED, "yoho_logmel: kernels exist for n_fft=400, hop=160 (got %d, %d)", n_fft, hop);
+  if (fb->n_mels > kMaxMels) return fail(YOHO_ERR_UNSUPPORTED, "yoho_logmel: n_mels=%d, the kernel's output tile holds up to %d", fb->n_mels, kMaxMels);
   if (fb->n_bins != kBins) return fail(YOHO_ERR_INVALID, "yoho_logmel: filterbank has %d bins, n_fft=400 needs 201", fb->n_bins);
   if (fb->device != ctx->device) return fail(YOHO_ERR_INVALID, "yoho_logmel: filterbank lives on device %d, context on %d", fb->device, ctx->device);
   int frames = frames_of(n_samples, n_fft, hop);
@@ -388,8 +463,8 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
   if (norm != YOHO_NORM_NONE && (ws == nullptr || ws_bytes < need))
     return fail(YOHO_ERR_WORKSPACE, "yoho_logmel: workspace %zu < %zu bytes", ws_bytes, need);
 
-  static_assert(sizeof(FrontendSmem) <= 113 * 1024, "two CTAs per SM");
-  YOHO_CUDA_CHECK(cudaFuncSetAttribute(logmel_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FrontendSmem))));
+  static_assert(sizeof(FrontendSmem<T>) <= 113 * 1024, "two CTAs per SM");
+  YOHO_CUDA_CHECK(cudaFuncSetAttribute(logmel_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FrontendSmem<T>))));
   const int tiles = logmel_tiles(frames);
   float2* stats = static_cast<float2*>(ws);
   const int vec_ok = (n_samples % int(16 / sizeof(T)) == 0) && (reinterpret_cast<uintptr_t>(pcm) % 16 == 0);
@@ -399,9 +474,11 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
     int nb = batch - c0 < chunk ? batch - c0 : chunk;
     {
       ProfScope prof(stream, kProfFrontend, double(nb) * (double(n_samples) * sizeof(T) + double(elems) * sizeof(float)));
-      logmel_kernel<T><<<dim3(tiles, nb), kThreads, sizeof(FrontendSmem), stream>>>(
-          pcm, n_samples, total_samples, frames, c0, ctx->d_window, ctx->d_twiddle, fb->d_lo, fb->d_len, fb->d_weights,
-          fb->band_stride, fb->n_mels, out, stats, tiles, norm, vec_ok);
+      const long long items = (long long)nb * tiles;
+      const int grid = int(items < 2LL * ctx->num_sms ? items : 2LL * ctx->num_sms);
+      logmel_kernel<T><<<grid, kThreads, sizeof(FrontendSmem<T>), stream>>>(
+          pcm, n_samples, total_samples, frames, c0, int(items), ctx->d_window, ctx->d_twiddle, fb->d_bands, fb->d_weights,
+          fb->band_stride, fb->n_mels, fb->sched, out, stats, tiles, norm, vec_ok);
       YOHO_LAUNCH_CHECK("logmel_kernel");
     }
     if (norm != YOHO_NORM_NONE) {
