@@ -199,7 +199,7 @@ def main():
     ap.add_argument("--workload", default="small256", choices=sorted(WORKLOADS))
     ap.add_argument("--clips", type=int, default=0, help="override clips per GPU")
     ap.add_argument("--chunk", type=int, default=0, help="clips per kernel-sequence chunk on the device path (0 = whole batch)")
-    ap.add_argument("--e2e-chunk", type=int, default=32, help="clips per pipelined chunk on the host path")
+    ap.add_argument("--e2e-chunk", type=int, default=64, help="clips per pipelined chunk on the host path")
     ap.add_argument("--norm", default="reference", choices=["reference", "whisper"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -109,3 +109,18 @@ def test_shard_range_partitions():
         assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
         sizes = [b - a for a, b in spans]
         assert max(sizes) - min(sizes) <= 1
+
+
+def test_chunk_plan_partitions_the_batch():
+    """The host pipeline's chunk plan (yoho_b200.pipeline.chunk_plan) covers every clip once, in order, never
+    exceeds the staging size, and tapers only when the batch has four chunks to spare."""
+    from yoho_b200.pipeline import chunk_plan
+    for batch in (1, 7, 32, 127, 128, 130, 256, 1000):
+        for chunk in (1, 2, 5, 32, 64):
+            for taper in (False, True):
+                plan = chunk_plan(batch, chunk, taper)
+                assert plan[0][0] == 0 and sum(n for _, n in plan) == batch
+                assert all(0 < n <= chunk for _, n in plan)
+                assert all(plan[i][0] + plan[i][1] == plan[i + 1][0] for i in range(len(plan) - 1))
+    assert [n for _, n in chunk_plan(256, 32)] == [8, 24, 32, 32, 32, 32, 32, 32, 16, 8, 8]
+    assert [n for _, n in chunk_plan(64, 32)] == [32, 32]

@@ -1,6 +1,6 @@
 """DRAM traffic per launch of each kernel class from `ncu --set full` reports of tools/prof_case.py.
 
-    python tools/ncu_traffic.py <clips in the capture> gpurun_out/x_gemm.ncu-rep ... > profiles/traffic.json
+    python tools/ncu_traffic.py <clips in the capture>[:<clips of the captured log-mel launch>] gpurun_out/x_gemm.ncu-rep ... > profiles/traffic.json
 
 Writes {class: {"bytes_per_launch_per_clip": ..., "launches": n, "clips": c, "source": [...]}}; bench.py scales it
 by the clips of its own launches to fill roofline.traffic (dram__bytes_read.sum + dram__bytes_write.sum)."""
@@ -8,7 +8,10 @@ import csv, io, json, subprocess, sys
 
 CLASS = {"gemm_bf16_kernel": "gemm_tcgen05", "attention_bf16_kernel": "attention_tcgen05", "logmel_kernel": "logmel",
          "layernorm_kernel": "layernorm", "normalize_apply_kernel": "normalize"}
-clips = int(sys.argv[1])
+# the log-mel kernel is persistent (1-D grid), so the clips of the captured launch are given: prof_case.py runs it
+# over max(clips, 128) clips in launches of <= 52 (one L2-resident chunk), and the capture takes a full one
+clips, _, logmel_clips = sys.argv[1].partition(":")
+clips, logmel_clips = int(clips), int(logmel_clips or 52)
 out = {}
 for path in sys.argv[2:]:
     raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
@@ -21,10 +24,7 @@ for path in sys.argv[2:]:
         if name is None:
             continue
         total = sum(float(r[idx[m]]) * scale[units[idx[m]]] for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
-        # the log-mel capture runs over max(clips, 128) clips in launches of <= 52 (grid.y)
-        n_clips = clips
-        if name == "logmel":
-            n_clips = int(r[idx["Grid Size"]].strip("()").split(",")[1])
+        n_clips = logmel_clips if name == "logmel" else clips
         e = out.setdefault(name, {"bytes": 0.0, "launches": 0, "clips": n_clips, "source": []})
         e["bytes"] += total
         e["launches"] += 1

@@ -24,6 +24,26 @@ _NORM = {"none": NORM_NONE, "reference": NORM_REFERENCE, "whisper": NORM_WHISPER
 _COMPUTE = {"bf16": COMPUTE_BF16, "fp32": COMPUTE_FP32}
 
 
+def chunk_plan(batch: int, chunk: int, taper: bool = True) -> list[tuple[int, int]]:
+    """[(first clip, clips)] of the pipelined host path.  The copies of all but the first chunk's input and
+    the last chunk's output hide behind kernels, so with ``taper`` the first chunk is a quarter and the last
+    two are a half and a quarter of ``chunk`` (when the batch has at least four chunks to spare)."""
+    sizes: list[int] = []
+    q = chunk // 4
+    if taper and q >= 1 and batch >= 4 * chunk:
+        head, tail = [q, chunk - q], [chunk // 2, chunk - chunk // 2 - q, q]
+        body = batch - 2 * chunk
+        sizes = head + [chunk] * (body // chunk) + ([body % chunk] if body % chunk else []) + tail
+    else:
+        sizes = [chunk] * (batch // chunk) + ([batch % chunk] if batch % chunk else [])
+    plan, b0 = [], 0
+    for n in sizes:
+        plan.append((b0, n))
+        b0 += n
+    assert b0 == batch
+    return plan
+
+
 class ClipEncoder:
     """Log-mel + encoder over batches of fixed-length clips on one GPU.
 
@@ -100,14 +120,22 @@ class ClipEncoder:
                 self.encoder(mel, out[b0:b1])
         return out
 
+    def _reserve(self, batch: int) -> None:
+        """Size the grow-only scratch buffers for ``batch`` clips up front, so that no chunk of a pipelined
+        run reallocates one while kernels of the previous chunk still use it."""
+        lib = self.rt.lib
+        self._mel_buf(batch)
+        self.rt.workspace("logmel", lib.yoho_logmel_workspace_bytes(batch, self.n_samples, self.n_fft, self.hop, self.n_mels))
+        self.rt.workspace("encoder", lib.yoho_encoder_workspace_bytes(C.byref(self.desc), batch, self.frames, self.compute))
+
     # ---- host-facing path -------------------------------------------------------------------
     def host_buffers(self, batch: int, pcm_dtype: torch.dtype = torch.float32) -> tuple[torch.Tensor, torch.Tensor]:
         """Pinned host buffers shaped for ``encode_host``: PCM (batch, n_samples) and states (batch, seq_len, dims)."""
         return (torch.empty((batch, self.n_samples), dtype=pcm_dtype, pin_memory=True),
                 torch.empty((batch, self.seq_len, self.dims), dtype=torch.float32, pin_memory=True))
 
-    def encode_host(self, pcm_host: torch.Tensor, out_host: torch.Tensor | None = None, chunk_clips: int = 32,
-                    sync: bool = True) -> torch.Tensor:
+    def encode_host(self, pcm_host: torch.Tensor, out_host: torch.Tensor | None = None, chunk_clips: int = 64,
+                    sync: bool = True, taper: bool = True) -> torch.Tensor:
         """Host PCM -> host encoder states.  ``pcm_host``: CPU tensor / ndarray (B, n_samples), float32
         or int16; pinned memory makes the H2D copies asynchronous (pageable memory still works, the
         copies then serialise with the host).  Returns ``out_host`` (pinned unless supplied)."""
@@ -133,11 +161,12 @@ class ClipEncoder:
             ready.record(entry)
             for s in (s_in, s_run, s_out):
                 s.wait_event(ready)
+            with torch.cuda.stream(s_run):
+                self._reserve(chunk)
             ran: list = []
             drained: list = []
-            for i, b0 in enumerate(range(0, B, chunk)):
-                b1 = min(B, b0 + chunk)
-                n, slot = b1 - b0, i & 1
+            for i, (b0, n) in enumerate(chunk_plan(B, chunk, taper)):
+                b1, slot = b0 + n, i & 1
                 with torch.cuda.stream(s_in):
                     if i >= 2:
                         s_in.wait_event(ran[i - 2])            # staging slot is free again
