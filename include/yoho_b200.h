@@ -198,6 +198,64 @@ int yoho_crosskv_fwd(yoho_ctx* ctx, const yoho_crosskv_desc* desc, const void* b
                      int batch, int t, float* kv, int compute, void* ws, size_t ws_bytes,
                      yoho_stream_t stream);
 
+/* ---- Whisper text decoder with a KV cache -------------------------------- */
+
+/* TextDecoder(vocab_size, seq_len, dims, n_heads, n_layers) (whisper.py:138-165) plus the shape of the encoder
+ * states it attends to.  dims / n_heads must be 64.  float32 SIMT kernels throughout (1e-4 parity path): one
+ * generated token is `batch` rows against every weight, i.e. weight streaming, not tensor-core work. */
+typedef struct yoho_decoder_desc {
+  int32_t vocab;      /* rows of Embed_0.embedding, tied with the logits (whisper.py:153, :163) */
+  int32_t seq_len;    /* rows of positional_embedding = token buffer length (448)             */
+  int32_t dims;       /* D (text_dims)                                                          */
+  int32_t n_heads;
+  int32_t n_layers;
+  int32_t audio_dims; /* width of the encoder states                                            */
+  int32_t audio_len;  /* encoder positions per clip (1500)                                      */
+} yoho_decoder_desc;
+
+/* 4 + 24 * n_layers float32 tensors, Flax layouts, in order:
+ *   positional_embedding (seq_len, D), Embed_0.embedding (vocab, D), LayerNorm_0.scale, LayerNorm_0.bias (final, :162);
+ *   per DecoderBlock_l: LayerNorm_0.{scale,bias};
+ *     MultiHeadAttention_0 (masked self attention): query_proj.{kernel,bias}, key_proj.kernel, value_proj.{kernel,bias},
+ *     out_proj.{kernel,bias};  LayerNorm_1.{scale,bias};
+ *     MultiHeadAttention_1 (cross attention; key/value kernels are (audio_dims, D)): same seven;
+ *     LayerNorm_2.{scale,bias};  Dense_0.{kernel (D,4D), bias};  Dense_1.{kernel (4D,D), bias}. */
+int yoho_decoder_num_tensors(const yoho_decoder_desc* desc);
+size_t yoho_decoder_weights_bytes(const yoho_decoder_desc* desc);
+int yoho_decoder_weights_pack(yoho_ctx* ctx, const yoho_decoder_desc* desc, const float* const* tensors,
+                              int n_tensors, void* blob, size_t blob_bytes, yoho_stream_t stream);
+
+/* Teacher-forced forward == Whisper.decode_text(encoded_audio, tokens) (whisper.py:197-198 -> :147-165):
+ *   tokens (batch, s_len) int32, states (batch, audio_len, audio_dims) float32 -> logits (batch, s_len, vocab) float32.
+ * s_len <= seq_len.  Token ids outside [0, vocab) are clamped. */
+size_t yoho_decoder_workspace_bytes(const yoho_decoder_desc* desc, int batch, int s_len);
+int yoho_decoder_fwd(yoho_ctx* ctx, const yoho_decoder_desc* desc, const void* blob, const int32_t* tokens,
+                     const float* states, int batch, int s_len, float* logits, void* ws, size_t ws_bytes,
+                     yoho_stream_t stream);
+
+/* Token-by-token generation, the loop of whisper.py:260-285 with the KV cache the reference lacks (:27).
+ *   cache: yoho_decoder_cache_bytes(desc, batch) bytes, 1024-byte aligned: a device-side position counter, the self
+ *          attention keys / values of every layer (n_layers, batch, seq_len, 2D) and the cross attention keys / values
+ *          (n_layers, batch, audio_len, 2D).
+ *   yoho_decoder_begin   computes the cross keys / values from `states` once and sets the position to 0.
+ *   yoho_decoder_step    at position p (read on the device): consumes tokens[:, p], appends to the self cache, writes
+ *                        the logits for position p + 1 to `logits` (batch, vocab) if not NULL, stores their first argmax
+ *                        (jnp.argmax, :279) into tokens[:, p + 1] unless forced[p + 1] != 0 (forced: seq_len bytes on the
+ *                        device or NULL; the reference pre-fills positions 0, 2, 3, :266-272), and advances p.  A row
+ *                        whose token at p is `eot` keeps producing `eot` (pass eot < 0 to disable).
+ *   yoho_decoder_generate  n_steps such steps back to back (no host synchronisation; CUDA-graph capturable).
+ * tokens: (batch, seq_len) int32 on the device. */
+size_t yoho_decoder_cache_bytes(const yoho_decoder_desc* desc, int batch);
+size_t yoho_decoder_step_workspace_bytes(const yoho_decoder_desc* desc, int batch);
+int yoho_decoder_begin(yoho_ctx* ctx, const yoho_decoder_desc* desc, const void* blob, const float* states,
+                       int batch, void* cache, size_t cache_bytes, yoho_stream_t stream);
+int yoho_decoder_step(yoho_ctx* ctx, const yoho_decoder_desc* desc, const void* blob, int32_t* tokens, int batch,
+                      void* cache, size_t cache_bytes, float* logits, const unsigned char* forced, int eot,
+                      void* ws, size_t ws_bytes, yoho_stream_t stream);
+int yoho_decoder_generate(yoho_ctx* ctx, const yoho_decoder_desc* desc, const void* blob, int32_t* tokens,
+                          int batch, void* cache, size_t cache_bytes, const unsigned char* forced, int eot,
+                          int n_steps, void* ws, size_t ws_bytes, yoho_stream_t stream);
+
 /* ---- YOHO's own audio encoder (next row after the Whisper path) ------------------------ */
 
 /* Shape of AudioEncoder(q_heads, kv_heads, dims, seq_len, blocks) (yoho/src/nn/model.py:9-14) plus the mel

@@ -82,8 +82,8 @@ def test_argument_validation_like_the_reference():
         mel_spectogram(np.zeros(480000, np.float32), 400, 160, 16000, 80)
     with pytest.raises(ValueError):
         AudioEncoder(1500, 384, 6, 4).apply({"params": {}}, np.zeros((2999, 80), np.float32))
-    with pytest.raises(NotImplementedError):
-        Whisper(384, 1500, 6, 4).apply({"params": {}}, None, method=Whisper.decode_text)
+    with pytest.raises(ValueError):                      # built without text_* fields: no decoder to run
+        Whisper(384, 1500, 6, 4).apply({"params": {}}, None, None, method=Whisper.decode_text)
 
 
 def test_no_cpu_fallback():

@@ -35,6 +35,11 @@ class CrossKvDesc(C.Structure):
     _fields_ = [("d_in", C.c_int32), ("d_out", C.c_int32), ("n_layers", C.c_int32)]
 
 
+class DecoderDesc(C.Structure):
+    _fields_ = [("vocab", C.c_int32), ("seq_len", C.c_int32), ("dims", C.c_int32), ("n_heads", C.c_int32),
+                ("n_layers", C.c_int32), ("audio_dims", C.c_int32), ("audio_len", C.c_int32)]
+
+
 _p, _i, _sz = C.c_void_p, C.c_int, C.c_size_t
 
 # name -> (restype, argtypes); mirrors include/yoho_b200.h one to one
@@ -66,6 +71,16 @@ SIGNATURES = {
     "yoho_crosskv_weights_pack": (_i, [_p, C.POINTER(CrossKvDesc), C.POINTER(_p), _i, _p, _sz, _p]),
     "yoho_crosskv_workspace_bytes": (_sz, [C.POINTER(CrossKvDesc), _i, _i, _i]),
     "yoho_crosskv_fwd": (_i, [_p, C.POINTER(CrossKvDesc), _p, _p, _i, _i, _p, _i, _p, _sz, _p]),
+    "yoho_decoder_num_tensors": (_i, [C.POINTER(DecoderDesc)]),
+    "yoho_decoder_weights_bytes": (_sz, [C.POINTER(DecoderDesc)]),
+    "yoho_decoder_weights_pack": (_i, [_p, C.POINTER(DecoderDesc), C.POINTER(_p), _i, _p, _sz, _p]),
+    "yoho_decoder_workspace_bytes": (_sz, [C.POINTER(DecoderDesc), _i, _i]),
+    "yoho_decoder_fwd": (_i, [_p, C.POINTER(DecoderDesc), _p, _p, _p, _i, _i, _p, _p, _sz, _p]),
+    "yoho_decoder_cache_bytes": (_sz, [C.POINTER(DecoderDesc), _i]),
+    "yoho_decoder_step_workspace_bytes": (_sz, [C.POINTER(DecoderDesc), _i]),
+    "yoho_decoder_begin": (_i, [_p, C.POINTER(DecoderDesc), _p, _p, _i, _p, _sz, _p]),
+    "yoho_decoder_step": (_i, [_p, C.POINTER(DecoderDesc), _p, _p, _i, _p, _sz, _p, _p, _i, _p, _sz, _p]),
+    "yoho_decoder_generate": (_i, [_p, C.POINTER(DecoderDesc), _p, _p, _i, _p, _sz, _p, _i, _i, _p, _sz, _p]),
     "yoho_model_num_tensors": (_i, [C.POINTER(ModelDesc)]),
     "yoho_model_weights_bytes": (_sz, [C.POINTER(ModelDesc)]),
     "yoho_model_weights_pack": (_i, [_p, C.POINTER(ModelDesc), C.POINTER(_p), _i, _p, _sz, _p]),

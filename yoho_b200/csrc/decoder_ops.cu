@@ -1,0 +1,316 @@
+// Kernels of the Whisper text decoder's token-by-token path (reference yoho/src/nn/whisper.py:138-165 run with a
+// KV cache instead of the reference's full re-run per token, :27 / :274-281).  One generated token = M = batch
+// activation rows against every decoder weight, so each contraction is a weight-streaming "skinny" GEMM: the job
+// is to put the whole GPU's load/store units on a 1-4 MB weight matrix for a couple of microseconds, not to feed
+// tensor cores.  The decode position lives in device memory so that one launch sequence (or one CUDA graph) serves
+// every token.
+#include "kernels.cuh"
+
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
+
+namespace yoho {
+
+__device__ __forceinline__ float dec_gelu_tanh(float x) {
+  const float c = 0.7978845608028654f;
+  return 0.5f * x * (1.0f + tanhf(c * (x + 0.044715f * x * x * x)));
+}
+
+// ---- x[b, s, :] = embedding[token[b, p0 + s]] + positional_embedding[p0 + s]            whisper.py:153-155
+__global__ void __launch_bounds__(128)
+embed_kernel(const int* __restrict__ tokens, int tok_ld, const int* __restrict__ pos_ptr, int s_len,
+             const float* __restrict__ emb, const float* __restrict__ pos, float* __restrict__ x, int dims, int vocab) {
+  const int s = blockIdx.x, b = blockIdx.y;
+  const int p0 = pos_ptr ? *pos_ptr : 0;     // < tok_ld: advance_kernel saturates the counter
+  int tok = tokens[size_t(b) * tok_ld + p0 + s];
+  tok = tok < 0 ? 0 : (tok >= vocab ? vocab - 1 : tok);
+  const float4* e = reinterpret_cast<const float4*>(emb + size_t(tok) * dims);
+  const float4* p = reinterpret_cast<const float4*>(pos + size_t(p0 + s) * dims);
+  float4* o = reinterpret_cast<float4*>(x + (size_t(b) * s_len + s) * dims);
+  for (int i = threadIdx.x; i < dims / 4; i += blockDim.x) {
+    float4 a = __ldg(e + i), c = __ldg(p + i);
+    o[i] = make_float4(a.x + c.x, a.y + c.y, a.z + c.z, a.w + c.w);
+  }
+}
+
+int launch_embed(const int* tokens, int tok_ld, const int* pos_ptr, int batch, int s_len, const float* emb, const float* pos,
+                 float* x, int dims, int vocab, cudaStream_t s) {
+  if (batch <= 0 || s_len <= 0) return YOHO_OK;
+  if (dims % 4 != 0 || batch > 65535) return fail(YOHO_ERR_UNSUPPORTED, "embed: dims=%d batch=%d", dims, batch);
+  embed_kernel<<<dim3(s_len, batch), 128, 0, s>>>(tokens, tok_ld, pos_ptr, s_len, emb, pos, x, dims, vocab);
+  YOHO_LAUNCH_CHECK("embed_kernel");
+  return YOHO_OK;
+}
+
+// ---- skinny GEMM: out[b, n] (+)= act(sum_k x[b, k] w[k, n] + bias[n]), b < BT <= 64 ------------------------------
+// CTA = 32 output columns x the k-range of its cluster rank; its 8 warps take interleaved weight rows (one 128-byte
+// row segment per warp-load, eight loads in flight per warp), the activations of the k-range sit in shared memory
+// (k-major, 128-bit broadcast reads); partial sums are reduced across warps in shared memory and across the KS CTAs of
+// a thread-block cluster through distributed shared memory (deterministic: no atomics).
+constexpr int kSkThreads = 256, kSkWarps = 8, kSkCols = 32, kSkChunk = 256;
+
+template <int BT, int KS>
+__global__ void __launch_bounds__(kSkThreads)
+skinny_gemm_kernel(const SkinnyArgs a) {
+  extern __shared__ __align__(16) float sk_smem[];
+  float* xs = sk_smem;                                  // [kSkChunk][BT] (4-float groups xor-swizzled by k), later red[8][BT][32]
+  float* part = sk_smem + (kSkChunk * BT > kSkWarps * BT * 32 ? kSkChunk * BT : kSkWarps * BT * 32);   // [BT][32]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rank = KS > 1 ? int(blockIdx.y) : 0;
+  const int col = blockIdx.x * kSkCols + lane;
+  const bool col_ok = col < a.n;
+  const int k_per = (a.k + KS - 1) / KS;
+  const int k_begin = rank * k_per, k_end = min(a.k, k_begin + k_per);
+  constexpr int G = BT / 4;                             // 4-float groups per k row
+
+  float acc[BT];
+#pragma unroll
+  for (int b = 0; b < BT; ++b) acc[b] = 0.0f;
+
+  for (int k0 = k_begin; k0 < k_end; k0 += kSkChunk) {
+    const int len = min(kSkChunk, k_end - k0);
+    __syncthreads();
+    for (int idx = tid; idx < BT * kSkChunk; idx += kSkThreads) {
+      const int b = idx / kSkChunk, kk = idx - b * kSkChunk;
+      const float v = (b < a.b && kk < len) ? __ldg(a.x + size_t(b) * a.ldx + k0 + kk) : 0.0f;
+      xs[kk * BT + (((b >> 2) ^ (kk & (G - 1))) << 2) + (b & 3)] = v;
+    }
+    __syncthreads();
+    const float* wp = a.w + size_t(k0) * a.ldw + col;
+    for (int kk0 = warp; kk0 < len; kk0 += 8 * kSkWarps) {
+      float wv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int kk = kk0 + u * kSkWarps;
+        wv[u] = (col_ok && kk < len) ? __ldg(wp + size_t(kk) * a.ldw) : 0.0f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int kk = kk0 + u * kSkWarps;       // < kSkChunk by construction
+        const float4* xr = reinterpret_cast<const float4*>(xs + kk * BT);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          const float4 xv = xr[g ^ (kk & (G - 1))];
+          acc[4 * g + 0] = fmaf(xv.x, wv[u], acc[4 * g + 0]);
+          acc[4 * g + 1] = fmaf(xv.y, wv[u], acc[4 * g + 1]);
+          acc[4 * g + 2] = fmaf(xv.z, wv[u], acc[4 * g + 2]);
+          acc[4 * g + 3] = fmaf(xv.w, wv[u], acc[4 * g + 3]);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  float* red = xs;
+#pragma unroll
+  for (int b = 0; b < BT; ++b) red[(warp * BT + b) * 32 + lane] = acc[b];
+  __syncthreads();
+  for (int o = tid; o < BT * 32; o += kSkThreads) {
+    float v = 0.0f;
+#pragma unroll
+    for (int w = 0; w < kSkWarps; ++w) v += red[w * BT * 32 + o];
+    part[o] = v;
+  }
+  if (KS > 1) {
+    cg::cluster_group cluster = cg::this_cluster();
+    cluster.sync();
+    if (rank == 0) {
+      for (int o = tid; o < BT * 32; o += kSkThreads) {
+        float v = part[o];
+        for (int r = 1; r < KS; ++r) v += cluster.map_shared_rank(part, r)[o];
+        part[o] = v;
+      }
+    }
+    cluster.sync();          // the peers' shared memory stays alive until rank 0 has read it
+    if (rank != 0) return;
+  }
+  __syncthreads();
+  const long long row_off = a.row_off_ptr ? (long long)(*a.row_off_ptr) * a.row_off_mul : 0;
+  for (int o = tid; o < BT * 32; o += kSkThreads) {
+    const int b = o >> 5, c = blockIdx.x * kSkCols + (o & 31);
+    if (b >= a.b || c >= a.n) continue;
+    float v = part[o];
+    if (a.bias) v += __ldg(a.bias + c);
+    if (a.gelu) v = dec_gelu_tanh(v);
+    float* dst = a.out + (long long)b * a.out_row_stride + row_off + c;
+    *dst = a.accumulate ? *dst + v : v;
+  }
+}
+
+template <int BT, int KS>
+static int skinny_launch(const SkinnyArgs& a, cudaStream_t s) {
+  const size_t main_floats = size_t(kSkChunk) * BT > size_t(kSkWarps) * BT * 32 ? size_t(kSkChunk) * BT : size_t(kSkWarps) * BT * 32;
+  const size_t smem = (main_floats + size_t(BT) * 32) * sizeof(float);
+  YOHO_CUDA_CHECK(cudaFuncSetAttribute(skinny_gemm_kernel<BT, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ceil_div(a.n, kSkCols), KS, 1);
+  cfg.blockDim = dim3(kSkThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = KS; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  YOHO_CUDA_CHECK(cudaLaunchKernelEx(&cfg, skinny_gemm_kernel<BT, KS>, a));
+  YOHO_LAUNCH_CHECK("skinny_gemm_kernel");
+  return YOHO_OK;
+}
+
+int launch_skinny_gemm(const SkinnyArgs& a, cudaStream_t s) {
+  if (a.b <= 0 || a.n <= 0 || a.k <= 0) return YOHO_OK;
+  if (a.b > 64) return fail(YOHO_ERR_UNSUPPORTED, "skinny gemm: %d rows (<= 64 per call)", a.b);
+  // enough column blocks to fill the GPU on their own (the vocabulary projection): no k split
+  const bool wide = ceil_div(a.n, kSkCols) >= 296;
+  ProfScope prof(s, kProfOther, 2.0 * a.b * double(a.n) * a.k);
+#define YOHO_SK(BT)                                                          \
+  return wide ? skinny_launch<BT, 1>(a, s) : skinny_launch<BT, 8>(a, s)
+  if (a.b <= 4) { YOHO_SK(4); }
+  if (a.b <= 8) { YOHO_SK(8); }
+  if (a.b <= 16) { YOHO_SK(16); }
+  if (a.b <= 32) { YOHO_SK(32); }
+  YOHO_SK(64);
+#undef YOHO_SK
+}
+
+// ---- single-query attention against a key/value cache --------------------------------------------------------------
+// grid (heads, batch); one query row per CTA.  scores = (q . k_j) / 8 (q and k each carry 64^-0.25, whisper.py:54-57),
+// softmax over the first `len` cache rows, out = sum_j p_j v_j.  `len` comes from device memory for the growing
+// self-attention cache (position + 1) or is the constant number of encoder positions for the cross attention.
+constexpr int kDaThreads = 256;
+
+__global__ void __launch_bounds__(kDaThreads)
+decode_attention_kernel(const DecodeAttArgs a) {
+  extern __shared__ float da_smem[];
+  float* sc = da_smem;                       // [len]
+  __shared__ float red[kDaThreads / 32];
+  __shared__ float part[4][64];
+  const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int len = a.len_ptr ? *a.len_ptr + a.len_add : a.len_const;
+  const float* kv = a.kv + (long long)b * a.kv_clip_stride + h * 64;
+  const float2 q2 = __ldg(reinterpret_cast<const float2*>(a.q + size_t(b) * a.ldq + h * 64) + lane);
+
+  for (int j0 = warp; j0 < len; j0 += 4 * (kDaThreads / 32)) {
+    float d[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int j = j0 + u * (kDaThreads / 32);
+      float2 k2 = make_float2(0.0f, 0.0f);
+      if (j < len) k2 = __ldg(reinterpret_cast<const float2*>(kv + size_t(j) * a.kv_ld + a.k_off) + lane);
+      d[u] = fmaf(q2.x, k2.x, q2.y * k2.y);
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1)
+#pragma unroll
+      for (int u = 0; u < 4; ++u) d[u] += __shfl_xor_sync(0xffffffffu, d[u], o);
+    if (lane == 0)
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = j0 + u * (kDaThreads / 32);
+        if (j < len) sc[j] = d[u] * 0.125f;
+      }
+  }
+  __syncthreads();
+  float mx = -INFINITY;
+  for (int j = tid; j < len; j += kDaThreads) mx = fmaxf(mx, sc[j]);
+#pragma unroll
+  for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0) red[warp] = mx;
+  __syncthreads();
+  mx = red[0];
+#pragma unroll
+  for (int w = 1; w < kDaThreads / 32; ++w) mx = fmaxf(mx, red[w]);
+  __syncthreads();
+  float sum = 0.0f;
+  for (int j = tid; j < len; j += kDaThreads) {
+    const float e = expf(sc[j] - mx);
+    sc[j] = e;
+    sum += e;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) red[warp] = sum;
+  __syncthreads();
+  sum = 0.0f;
+#pragma unroll
+  for (int w = 0; w < kDaThreads / 32; ++w) sum += red[w];
+  const int slice = tid >> 6, dcol = tid & 63;
+  const float* vp = kv + a.v_off + dcol;
+  float o0 = 0.0f, o1 = 0.0f, o2 = 0.0f, o3 = 0.0f;
+  int j = slice;
+  for (; j + 12 < len; j += 16) {
+    o0 = fmaf(sc[j], __ldg(vp + size_t(j) * a.kv_ld), o0);
+    o1 = fmaf(sc[j + 4], __ldg(vp + size_t(j + 4) * a.kv_ld), o1);
+    o2 = fmaf(sc[j + 8], __ldg(vp + size_t(j + 8) * a.kv_ld), o2);
+    o3 = fmaf(sc[j + 12], __ldg(vp + size_t(j + 12) * a.kv_ld), o3);
+  }
+  for (; j < len; j += 4) o0 = fmaf(sc[j], __ldg(vp + size_t(j) * a.kv_ld), o0);
+  part[slice][dcol] = (o0 + o1) + (o2 + o3);
+  __syncthreads();
+  if (tid < 64) a.out[size_t(b) * a.ldo + h * 64 + tid] = ((part[0][tid] + part[1][tid]) + (part[2][tid] + part[3][tid])) / sum;
+}
+
+int launch_decode_attention(const DecodeAttArgs& a, int batch, int heads, int max_len, cudaStream_t s) {
+  if (batch <= 0 || heads <= 0) return YOHO_OK;
+  if (batch > 65535) return fail(YOHO_ERR_UNSUPPORTED, "decode attention: batch=%d", batch);
+  const size_t smem = size_t(max_len) * sizeof(float);
+  if (smem > 200 * 1024) return fail(YOHO_ERR_UNSUPPORTED, "decode attention: %d cache rows exceed shared memory", max_len);
+  YOHO_CUDA_CHECK(cudaFuncSetAttribute(decode_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  ProfScope prof(s, kProfOther, 4.0 * batch * heads * 64.0 * max_len);
+  decode_attention_kernel<<<dim3(heads, batch), kDaThreads, smem, s>>>(a);
+  YOHO_LAUNCH_CHECK("decode_attention_kernel");
+  return YOHO_OK;
+}
+
+// ---- greedy choice: tokens[b, p + 1] = argmax_v logits[b, v] unless that position is forced ---------------------------
+// First maximum wins (jnp.argmax, whisper.py:279).  A sequence that has produced `eot` keeps producing it.
+__global__ void __launch_bounds__(256)
+greedy_pick_kernel(const float* __restrict__ logits, int ld, int vocab, int* __restrict__ tokens, int tok_ld, int max_len,
+                   const int* __restrict__ pos_ptr, const unsigned char* __restrict__ forced, int eot) {
+  __shared__ float bv[8];
+  __shared__ int bi[8];
+  const int b = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int p = *pos_ptr;
+  if (p + 1 >= max_len || (forced && forced[p + 1])) return;
+  const float* row = logits + size_t(b) * ld;
+  float best = -INFINITY;
+  int idx = 0x7fffffff;
+  for (int v = tid; v < vocab; v += 256) {
+    const float x = row[v];
+    if (x > best) { best = x; idx = v; }
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+    if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
+  }
+  if (lane == 0) { bv[warp] = best; bi[warp] = idx; }
+  __syncthreads();
+  if (tid == 0) {
+    for (int w = 1; w < 8; ++w)
+      if (bv[w] > best || (bv[w] == best && bi[w] < idx)) { best = bv[w]; idx = bi[w]; }
+    int* t = tokens + size_t(b) * tok_ld;
+    t[p + 1] = (eot >= 0 && t[p] == eot) ? eot : idx;
+  }
+}
+
+// the counter saturates at the last slot of the token buffer, so a step past the end rewrites that slot instead of
+// running off the caches
+__global__ void advance_kernel(int* pos_ptr, int max_len) { *pos_ptr = min(*pos_ptr + 1, max_len - 1); }
+
+int launch_greedy_pick(const float* logits, int ld, int vocab, int* tokens, int tok_ld, int max_len, int batch, int* pos_ptr,
+                       const unsigned char* forced, int eot, cudaStream_t s) {
+  if (batch <= 0) return YOHO_OK;
+  greedy_pick_kernel<<<batch, 256, 0, s>>>(logits, ld, vocab, tokens, tok_ld, max_len, pos_ptr, forced, eot);
+  YOHO_LAUNCH_CHECK("greedy_pick_kernel");
+  return YOHO_OK;
+}
+
+int launch_advance(int* pos_ptr, int max_len, cudaStream_t s) {
+  advance_kernel<<<1, 1, 0, s>>>(pos_ptr, max_len);
+  YOHO_LAUNCH_CHECK("advance_kernel");
+  return YOHO_OK;
+}
+
+}  // namespace yoho

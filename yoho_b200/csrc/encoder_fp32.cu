@@ -158,11 +158,16 @@ int launch_sgemm(const SgemmArgs& a, cudaStream_t s) {
 
 // In-place softmax over the last axis, one warp per row (whisper.py:64).
 __global__ void __launch_bounds__(256)
-softmax_rows_kernel(float* __restrict__ x, long long rows, int cols) {
+softmax_rows_kernel(float* __restrict__ x, long long rows, int cols_all, int causal_period) {
   long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
-  float* p = x + row * cols;
+  float* p = x + row * cols_all;
+  int cols = cols_all;
+  if (causal_period > 0) {                      // masked scores are -inf -> probability 0 (whisper.py:59-60, :157)
+    cols = min(cols_all, int(row % causal_period) + 1);
+    for (int i = cols + lane; i < cols_all; i += 32) p[i] = 0.0f;
+  }
   float mx = -INFINITY;
   for (int i = lane; i < cols; i += 32) mx = fmaxf(mx, p[i]);
 #pragma unroll
@@ -179,11 +184,11 @@ softmax_rows_kernel(float* __restrict__ x, long long rows, int cols) {
   for (int i = lane; i < cols; i += 32) p[i] *= inv;
 }
 
-int launch_softmax_rows(float* x, long long rows, int cols, cudaStream_t s) {
+int launch_softmax_rows(float* x, long long rows, int cols, cudaStream_t s, int causal_period) {
   if (rows == 0) return YOHO_OK;
   long long blocks = (rows + 7) / 8;
   if (blocks > 0x7fffffffLL) return fail(YOHO_ERR_UNSUPPORTED, "softmax: %lld rows", rows);
-  softmax_rows_kernel<<<unsigned(blocks), 256, 0, s>>>(x, rows, cols);
+  softmax_rows_kernel<<<unsigned(blocks), 256, 0, s>>>(x, rows, cols, causal_period);
   YOHO_LAUNCH_CHECK("softmax_rows_kernel");
   return YOHO_OK;
 }

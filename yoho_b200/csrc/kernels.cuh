@@ -51,7 +51,33 @@ struct SgemmArgs {
   int accumulate = 0;
 };
 int launch_sgemm(const SgemmArgs& a, cudaStream_t s);
-int launch_softmax_rows(float* x, long long rows, int cols, cudaStream_t s);
+// in-place softmax over the last axis; causal_period > 0: row r only sees columns <= r % causal_period (the
+// triu(-inf, 1) mask of whisper.py:157), the rest become 0
+int launch_softmax_rows(float* x, long long rows, int cols, cudaStream_t s, int causal_period = 0);
+
+// ---------------------------------------------------------------- decoder_ops.cu (token-by-token text decoder)
+int launch_embed(const int* tokens, int tok_ld, const int* pos_ptr, int batch, int s_len, const float* emb, const float* pos,
+                 float* x, int dims, int vocab, cudaStream_t s);
+struct SkinnyArgs {
+  const float* x = nullptr; int ldx = 0;            // (b, k) activations
+  const float* w = nullptr; int ldw = 0;            // (k, n) row-major weights (the Flax kernel layout)
+  const float* bias = nullptr;                      // (n) or null
+  float* out = nullptr; long long out_row_stride = 0;
+  const int* row_off_ptr = nullptr; int row_off_mul = 0;   // out += *row_off_ptr * row_off_mul (append at the device-side position)
+  int b = 0, k = 0, n = 0;
+  int gelu = 0, accumulate = 0;
+};
+int launch_skinny_gemm(const SkinnyArgs& a, cudaStream_t s);
+struct DecodeAttArgs {
+  const float* q = nullptr; int ldq = 0;            // (batch, heads * 64)
+  const float* kv = nullptr; long long kv_clip_stride = 0; int kv_ld = 0; int k_off = 0, v_off = 0;   // cache rows [.. k .. v ..]
+  const int* len_ptr = nullptr; int len_add = 0; int len_const = 0;
+  float* out = nullptr; int ldo = 0;
+};
+int launch_decode_attention(const DecodeAttArgs& a, int batch, int heads, int max_len, cudaStream_t s);
+int launch_greedy_pick(const float* logits, int ld, int vocab, int* tokens, int tok_ld, int max_len, int batch, int* pos_ptr,
+                       const unsigned char* forced, int eot, cudaStream_t s);
+int launch_advance(int* pos_ptr, int max_len, cudaStream_t s);
 
 // ---------------------------------------------------------------- gemm_sm100.cu (tcgen05)
 struct TapSpec { int col_off; int row_off; };

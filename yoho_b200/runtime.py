@@ -92,7 +92,8 @@ class Runtime:
     # ---- encoder weights ------------------------------------------------------------------
     def packed_weights(self, params: dict, desc, tensors: list, family: str = "encoder"):
         """Pack (once per params object) the float32 tensors into the device blob the kernels read.
-        ``family``: "encoder" (yoho_encoder_*: Whisper AudioEncoder) or "model" (yoho_model_*: YOHO's own encoder)."""
+        ``family``: "encoder" (yoho_encoder_*: Whisper AudioEncoder), "model" (yoho_model_*: YOHO's own encoder),
+        "crosskv" (yoho_crosskv_*) or "decoder" (yoho_decoder_*: Whisper TextDecoder)."""
         key = (family, id(params))
         hit = self._weights.get(key)
         if hit is not None and hit[0] is params:
