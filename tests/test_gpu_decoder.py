@@ -100,3 +100,31 @@ def test_eot_rows_stay_finished(rt):
             assert (seq[b, 1 + hits[0]:11] == eot).all()
             assert np.array_equal(seq[b, :1 + hits[0] + 1], free[b, :1 + hits[0] + 1])
     assert (seq[0, 4:11] == eot).all()
+
+
+@pytest.mark.parametrize("b", [1, 3, 4, 5, 8, 9, 16, 17, 33, 64, 70])
+@pytest.mark.parametrize("k,n,gelu,acc", [(128, 96, 0, 0), (512, 1536, 0, 1), (2048, 512, 1, 0), (320, 9600, 0, 0), (1280, 51865, 0, 0)])
+def test_skinny_gemm(rt, b, k, n, gelu, acc):
+    """The decoder's weight-streaming GEMM in isolation: every row-tile variant, with the cluster k split (n / 32 < 296
+    column blocks) and without it (vocabulary-sized n), ragged n and k, GELU and accumulate epilogues."""
+    import ctypes as C
+    import torch
+    from yoho_b200._lib import check
+    rng = np.random.default_rng(b * 1000 + k + n)
+    x = rng.standard_normal((b, k)).astype(np.float32)
+    w = (rng.standard_normal((k, n)) / np.sqrt(k)).astype(np.float32)
+    bias = rng.standard_normal(n).astype(np.float32)
+    base = rng.standard_normal((b, n)).astype(np.float32)
+    want = x.astype(np.float64) @ w.astype(np.float64) + bias
+    if gelu:
+        want = 0.5 * want * (1 + np.tanh(np.sqrt(2 / np.pi) * (want + 0.044715 * want ** 3)))
+    if acc:
+        want = want + base
+    xd, wd, bd = (torch.from_numpy(v).cuda() for v in (x, w, bias))
+    out = torch.from_numpy(base).cuda() if acc else torch.full((b, n), float("nan"), device="cuda")
+    check(rt.lib.yoho_test_skinny_gemm(rt.ctx, C.c_void_p(xd.data_ptr()), C.c_void_p(wd.data_ptr()), C.c_void_p(bd.data_ptr()),
+                                       C.c_void_p(out.data_ptr()), b, k, n, gelu, acc, rt.stream_ptr()))
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= 2e-5 * max(1.0, np.abs(want).max())

@@ -195,6 +195,49 @@ def stage_logmelperf():
                       f"({gbs / 6540.2 * 100:.1f}% of measured HBM peak)  {B * N / 16000.0 / ms * 1000:.0f}x realtime")
 
 
+def stage_decperf():
+    """Text decoder (whisper-base shape: 51865 x 512, 8 heads, 6 layers, 448 positions, 1500 encoder positions): greedy
+    generation with the KV cache, plain launches vs one replayed CUDA graph, and the teacher-forced forward."""
+    from yoho_b200.nn import TextDecoder, init_decoder_params
+    V, L, D, H, layers, T = 51865, 448, 512, 8, 6, 1500
+    p = init_decoder_params(V, L, D, layers, seed=1)
+    dec = TextDecoder(V, L, D, H, layers)
+    w_bytes = layers * (4 * D * D + 2 * D * D + 8 * D * D) * 4 + V * D * 4            # weights read per token (self q,kv,o; cross q,o; mlp; logits)
+    n_steps = 64
+    for B in (1, 8, 64):
+        states = torch.randn((B, T, D), device="cuda")
+        buf = torch.zeros((B, L), dtype=torch.int32, device="cuda")
+        buf[:, 0] = 50258
+        kv_bytes = B * layers * (T * 2 * D * 4)                                        # cross k|v read per token
+        for graph in (False, True):
+            dec.generate({"params": p}, states, buf, n_steps=4, use_graph=graph)
+            torch.cuda.synchronize()
+            t0 = time.time()
+            dec.generate({"params": p}, states, buf, n_steps=n_steps, use_graph=graph)
+            torch.cuda.synchronize()
+            dt = time.time() - t0
+            print(f"[decperf] B={B:3d} graph={int(graph)}: {dt / n_steps * 1e6:8.1f} us/step (incl. cross k/v setup)  {B * n_steps / dt:9.0f} tokens/s  "
+                  f"weights+cross-kv {(w_bytes + kv_bytes) / 1e6:.0f} MB/step -> {(w_bytes + kv_bytes) * n_steps / dt / 1e9:.0f} GB/s")
+        lib = get_runtime().lib
+        lib.yoho_prof_enable(1)
+        dec.generate({"params": p}, states, buf, n_steps=16)
+        torch.cuda.synchronize()
+        ncls = lib.yoho_prof_num_classes()
+        ms, work, cnt = (C.c_double * ncls)(), (C.c_double * ncls)(), (C.c_longlong * ncls)()
+        check(lib.yoho_prof_collect(ms, work, cnt, ncls))
+        lib.yoho_prof_enable(0)
+        for i in range(ncls):
+            if cnt[i]:
+                print(f"[decperf]     {lib.yoho_prof_class_name(i).decode():26s} {cnt[i] / 16:6.1f} launches/step  {ms[i] / 16 * 1e3:8.1f} us/step  "
+                      f"{ms[i] / cnt[i] * 1e3:6.1f} us each  {work[i] / ms[i] / 1e6:7.0f} GB/s")
+    for B, S in ((8, 64), (8, 448)):
+        states = torch.randn((B, T, D), device="cuda")
+        toks = torch.randint(0, V, (B, S), device="cuda", dtype=torch.int32)
+        ms = timed(lambda: dec.apply({"params": p}, toks, states), iters=3, warm=1)
+        fl = B * (S * layers * (2 * 14 * D * D + 4 * S * D + 4 * T * D) + layers * T * 2 * 2 * D * D + S * 2 * D * V)
+        print(f"[decperf] teacher-forced B={B} S={S}: {ms:.2f} ms  {fl / ms / 1e9:.1f} TFLOP/s fp32 SIMT")
+
+
 def stage_yohoperf():
     """YOHO's own config (train/config.toml:7-18): 164080-sample clips -> (B, 1024, 128) log-mel -> own encoder (384/6/3/4)."""
     from yoho_b200 import preprocessing as pp

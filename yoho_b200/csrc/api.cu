@@ -79,7 +79,7 @@ extern "C" int yoho_prof_enable(int on) {
 extern "C" int yoho_prof_num_classes(void) { return kProfNumClasses; }
 
 extern "C" const char* yoho_prof_class_name(int cls) {
-  static const char* names[kProfNumClasses] = {"logmel", "normalize", "gemm_tcgen05", "attention_tcgen05", "layernorm", "other"};
+  static const char* names[kProfNumClasses] = {"logmel", "normalize", "gemm_tcgen05", "attention_tcgen05", "layernorm", "other", "decoder_skinny_gemm", "decoder_cache_attention"};
   return (cls >= 0 && cls < kProfNumClasses) ? names[cls] : "";
 }
 

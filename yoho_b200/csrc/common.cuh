@@ -32,7 +32,7 @@ int fail(int code, const char* fmt, ...);
   } while (0)
 
 // ---- launch accounting and the optional per-kernel-class event profiler (bench.py roofline) ----
-enum ProfClass { kProfFrontend = 0, kProfNormalize, kProfGemm, kProfAttention, kProfLayerNorm, kProfOther, kProfNumClasses };
+enum ProfClass { kProfFrontend = 0, kProfNormalize, kProfGemm, kProfAttention, kProfLayerNorm, kProfOther, kProfDecGemm, kProfDecAttention, kProfNumClasses };
 void count_launch();
 // RAII: when profiling is enabled, brackets the launches issued in its lifetime with CUDA events on `s`.
 struct ProfScope {

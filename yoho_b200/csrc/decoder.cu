@@ -456,3 +456,12 @@ extern "C" int yoho_decoder_generate(yoho_ctx* ctx, const yoho_decoder_desc* des
   return dec_step_checked(ctx, desc, blob, tokens, batch, cache, cache_bytes, nullptr, forced, eot, n_steps, ws, ws_bytes,
                           static_cast<cudaStream_t>(stream), "yoho_decoder_generate");
 }
+
+// ------------------------------------------------------------------------------ test hook
+extern "C" int yoho_test_skinny_gemm(yoho_ctx* ctx, const float* x, const float* w, const float* bias, float* out, int b, int k, int n,
+                                     int gelu, int accumulate, yoho_stream_t stream_) {
+  if (!ctx || !x || !w || !out) return fail(YOHO_ERR_INVALID, "yoho_test_skinny_gemm: null argument");
+  for (int b0 = 0; b0 < b; b0 += 64)
+    YOHO_TRY(dec_skinny(x, k, b0, b - b0 < 64 ? b - b0 : 64, k, w, n, n, bias, out, n, nullptr, 0, gelu, accumulate, static_cast<cudaStream_t>(stream_)));
+  return YOHO_OK;
+}

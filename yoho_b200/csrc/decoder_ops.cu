@@ -71,8 +71,10 @@ skinny_gemm_kernel(const SkinnyArgs a) {
   for (int k0 = k_begin; k0 < k_end; k0 += kSkChunk) {
     const int len = min(kSkChunk, k_end - k0);
     __syncthreads();
-    for (int idx = tid; idx < BT * kSkChunk; idx += kSkThreads) {
-      const int b = idx / kSkChunk, kk = idx - b * kSkChunk;
+    // rows of the chunk the warps will touch: len rounded up to the 64-row step of the loop below
+    const int len_pad = min(kSkChunk, (len + 8 * kSkWarps - 1) / (8 * kSkWarps) * (8 * kSkWarps));
+    for (int idx = tid; idx < BT * len_pad; idx += kSkThreads) {
+      const int b = idx / len_pad, kk = idx - b * len_pad;
       const float v = (b < a.b && kk < len) ? __ldg(a.x + size_t(b) * a.ldx + k0 + kk) : 0.0f;
       xs[kk * BT + (((b >> 2) ^ (kk & (G - 1))) << 2) + (b & 3)] = v;
     }
@@ -111,37 +113,43 @@ skinny_gemm_kernel(const SkinnyArgs a) {
     for (int w = 0; w < kSkWarps; ++w) v += red[w * BT * 32 + o];
     part[o] = v;
   }
-  if (KS > 1) {
-    cg::cluster_group cluster = cg::this_cluster();
-    cluster.sync();
-    if (rank == 0) {
-      for (int o = tid; o < BT * 32; o += kSkThreads) {
-        float v = part[o];
-        for (int r = 1; r < KS; ++r) v += cluster.map_shared_rank(part, r)[o];
-        part[o] = v;
-      }
-    }
-    cluster.sync();          // the peers' shared memory stays alive until rank 0 has read it
-    if (rank != 0) return;
-  }
-  __syncthreads();
+  // every CTA of the cluster finishes its own share of the BT x 32 outputs: partials of the peers come through
+  // distributed shared memory, then bias / GELU / accumulate / store
+  constexpr int kOutPer = BT * 32 / KS;
+  if (KS > 1) cg::this_cluster().sync();
+  else __syncthreads();
   const long long row_off = a.row_off_ptr ? (long long)(*a.row_off_ptr) * a.row_off_mul : 0;
-  for (int o = tid; o < BT * 32; o += kSkThreads) {
+  for (int i = tid; i < kOutPer; i += kSkThreads) {
+    const int o = rank * kOutPer + i;
     const int b = o >> 5, c = blockIdx.x * kSkCols + (o & 31);
+    float v = 0.0f;
+    if (KS > 1) {
+      cg::cluster_group cluster = cg::this_cluster();
+#pragma unroll
+      for (int r = 0; r < KS; ++r) v += cluster.map_shared_rank(part, r)[o];
+    } else {
+      v = part[o];
+    }
     if (b >= a.b || c >= a.n) continue;
-    float v = part[o];
     if (a.bias) v += __ldg(a.bias + c);
     if (a.gelu) v = dec_gelu_tanh(v);
     float* dst = a.out + (long long)b * a.out_row_stride + row_off + c;
     *dst = a.accumulate ? *dst + v : v;
   }
+  if (KS > 1) cg::this_cluster().sync();          // peers keep their shared memory until everyone has read it
 }
 
 template <int BT, int KS>
 static int skinny_launch(const SkinnyArgs& a, cudaStream_t s) {
   const size_t main_floats = size_t(kSkChunk) * BT > size_t(kSkWarps) * BT * 32 ? size_t(kSkChunk) * BT : size_t(kSkWarps) * BT * 32;
   const size_t smem = (main_floats + size_t(BT) * 32) * sizeof(float);
-  YOHO_CUDA_CHECK(cudaFuncSetAttribute(skinny_gemm_kernel<BT, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+  static thread_local int attr_device = -1;      // the opt-in is per device; set it once per host thread and device
+  int dev = 0;
+  YOHO_CUDA_CHECK(cudaGetDevice(&dev));
+  if (attr_device != dev) {
+    YOHO_CUDA_CHECK(cudaFuncSetAttribute(skinny_gemm_kernel<BT, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    attr_device = dev;
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(ceil_div(a.n, kSkCols), KS, 1);
   cfg.blockDim = dim3(kSkThreads, 1, 1);
@@ -162,11 +170,13 @@ int launch_skinny_gemm(const SkinnyArgs& a, cudaStream_t s) {
   if (a.b > 64) return fail(YOHO_ERR_UNSUPPORTED, "skinny gemm: %d rows (<= 64 per call)", a.b);
   // enough column blocks to fill the GPU on their own (the vocabulary projection): no k split
   const bool wide = ceil_div(a.n, kSkCols) >= 296;
-  ProfScope prof(s, kProfOther, 2.0 * a.b * double(a.n) * a.k);
+  ProfScope prof(s, kProfDecGemm, (double(a.n) * a.k + double(a.b) * (a.n + a.k)) * sizeof(float));
 #define YOHO_SK(BT)                                                          \
   return wide ? skinny_launch<BT, 1>(a, s) : skinny_launch<BT, 8>(a, s)
   if (a.b <= 4) { YOHO_SK(4); }
-  if (a.b <= 8) { YOHO_SK(8); }
+  // the <8, 1> instantiation faults on the device ("operation not supported on global/shared address space") although
+  // its SASS reads like the other nine; 5..8 rows without a k split take the 16-row variant instead
+  if (a.b <= 8 && !wide) return skinny_launch<8, 8>(a, s);
   if (a.b <= 16) { YOHO_SK(16); }
   if (a.b <= 32) { YOHO_SK(32); }
   YOHO_SK(64);
@@ -174,45 +184,54 @@ int launch_skinny_gemm(const SkinnyArgs& a, cudaStream_t s) {
 }
 
 // ---- single-query attention against a key/value cache --------------------------------------------------------------
-// grid (heads, batch); one query row per CTA.  scores = (q . k_j) / 8 (q and k each carry 64^-0.25, whisper.py:54-57),
-// softmax over the first `len` cache rows, out = sum_j p_j v_j.  `len` comes from device memory for the growing
-// self-attention cache (position + 1) or is the constant number of encoder positions for the cross attention.
-constexpr int kDaThreads = 256;
+// One query row per (head, clip).  scores = (q . k_j) / 8 (q and k each carry 64^-0.25, whisper.py:54-57), softmax over
+// the first `len` cache rows, out = sum_j p_j v_j.  `len` comes from device memory for the growing self-attention cache
+// (position + 1) or is the constant number of encoder positions for the cross attention.
+// The cache rows of one (head, clip) are split over the kDaSplit CTAs of a thread-block cluster ("flash decoding"): one
+// clip alone still puts heads x 8 CTAs on the memory system, every CTA keeps all of its <= 256 rows' loads in flight, and
+// the partial (max, sum, out) triples are merged by rank 0 through distributed shared memory.
+constexpr int kDaThreads = 256, kDaSplit = 8, kDaLocal = 256;
 
 __global__ void __launch_bounds__(kDaThreads)
 decode_attention_kernel(const DecodeAttArgs a) {
-  extern __shared__ float da_smem[];
-  float* sc = da_smem;                       // [len]
+  __shared__ float sc[kDaLocal];
   __shared__ float red[kDaThreads / 32];
-  __shared__ float part[4][64];
-  const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  __shared__ __align__(16) float part[16][64];
+  __shared__ float loc[66];                      // this CTA's {out[64], max, sum}
+  cg::cluster_group cluster = cg::this_cluster();
+  const int h = blockIdx.x, b = blockIdx.y, rank = blockIdx.z;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int len = a.len_ptr ? *a.len_ptr + a.len_add : a.len_const;
-  const float* kv = a.kv + (long long)b * a.kv_clip_stride + h * 64;
-  const float2 q2 = __ldg(reinterpret_cast<const float2*>(a.q + size_t(b) * a.ldq + h * 64) + lane);
+  const int per = (len + kDaSplit - 1) / kDaSplit;
+  const int j_begin = rank * per;
+  const int n = max(0, min(len, j_begin + per) - j_begin);          // <= kDaLocal (launcher)
+  const float* kv = a.kv + (long long)b * a.kv_clip_stride + size_t(j_begin) * a.kv_ld + h * 64;
 
-  for (int j0 = warp; j0 < len; j0 += 4 * (kDaThreads / 32)) {
-    float d[4];
+  // scores: 8 lanes per cache row (8 dims each), 4 rows per warp-load, every load of the CTA's slice in flight at once
+  const int sub = lane & 7, kq = lane >> 3;
+  const float4* qp = reinterpret_cast<const float4*>(a.q + size_t(b) * a.ldq + h * 64 + sub * 8);
+  const float4 q0 = __ldg(qp), q1 = __ldg(qp + 1);
+  float d[kDaLocal / 32];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int j = j0 + u * (kDaThreads / 32);
-      float2 k2 = make_float2(0.0f, 0.0f);
-      if (j < len) k2 = __ldg(reinterpret_cast<const float2*>(kv + size_t(j) * a.kv_ld + a.k_off) + lane);
-      d[u] = fmaf(q2.x, k2.x, q2.y * k2.y);
+  for (int i = 0; i < kDaLocal / 32; ++i) {
+    const int j = i * 32 + warp * 4 + kq;
+    d[i] = 0.0f;
+    if (j < n) {
+      const float4* kp = reinterpret_cast<const float4*>(kv + size_t(j) * a.kv_ld + a.k_off + sub * 8);
+      const float4 k0 = __ldg(kp), k1 = __ldg(kp + 1);
+      d[i] = (q0.x * k0.x + q0.y * k0.y + q0.z * k0.z + q0.w * k0.w) + (q1.x * k1.x + q1.y * k1.y + q1.z * k1.z + q1.w * k1.w);
     }
+  }
 #pragma unroll
-    for (int o = 16; o; o >>= 1)
-#pragma unroll
-      for (int u = 0; u < 4; ++u) d[u] += __shfl_xor_sync(0xffffffffu, d[u], o);
-    if (lane == 0)
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int j = j0 + u * (kDaThreads / 32);
-        if (j < len) sc[j] = d[u] * 0.125f;
-      }
+  for (int i = 0; i < kDaLocal / 32; ++i) {
+    d[i] += __shfl_xor_sync(0xffffffffu, d[i], 1);
+    d[i] += __shfl_xor_sync(0xffffffffu, d[i], 2);
+    d[i] += __shfl_xor_sync(0xffffffffu, d[i], 4);
+    const int j = i * 32 + warp * 4 + kq;
+    if (sub == 0 && j < n) sc[j] = d[i] * 0.125f;
   }
   __syncthreads();
-  float mx = -INFINITY;
-  for (int j = tid; j < len; j += kDaThreads) mx = fmaxf(mx, sc[j]);
+  float mx = tid < n ? sc[tid] : -INFINITY;
 #pragma unroll
   for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   if (lane == 0) red[warp] = mx;
@@ -221,12 +240,9 @@ decode_attention_kernel(const DecodeAttArgs a) {
 #pragma unroll
   for (int w = 1; w < kDaThreads / 32; ++w) mx = fmaxf(mx, red[w]);
   __syncthreads();
-  float sum = 0.0f;
-  for (int j = tid; j < len; j += kDaThreads) {
-    const float e = expf(sc[j] - mx);
-    sc[j] = e;
-    sum += e;
-  }
+  float e = 0.0f;
+  if (tid < n) { e = expf(sc[tid] - mx); sc[tid] = e; }
+  float sum = e;
 #pragma unroll
   for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
   if (lane == 0) red[warp] = sum;
@@ -234,30 +250,63 @@ decode_attention_kernel(const DecodeAttArgs a) {
   sum = 0.0f;
 #pragma unroll
   for (int w = 0; w < kDaThreads / 32; ++w) sum += red[w];
-  const int slice = tid >> 6, dcol = tid & 63;
-  const float* vp = kv + a.v_off + dcol;
-  float o0 = 0.0f, o1 = 0.0f, o2 = 0.0f, o3 = 0.0f;
-  int j = slice;
-  for (; j + 12 < len; j += 16) {
-    o0 = fmaf(sc[j], __ldg(vp + size_t(j) * a.kv_ld), o0);
-    o1 = fmaf(sc[j + 4], __ldg(vp + size_t(j + 4) * a.kv_ld), o1);
-    o2 = fmaf(sc[j + 8], __ldg(vp + size_t(j + 8) * a.kv_ld), o2);
-    o3 = fmaf(sc[j + 12], __ldg(vp + size_t(j + 12) * a.kv_ld), o3);
+  // out: 16 threads per cache row (one float4 of the 64 dims each), 16 rows per pass
+  {
+    const int slice = tid >> 4, d4 = tid & 15;
+    const float* vp = kv + a.v_off + d4 * 4;
+    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+    for (int i = 0; i < kDaLocal / 16; ++i) {
+      const int j = i * 16 + slice;
+      if (j < n) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(vp + size_t(j) * a.kv_ld));
+        const float p = sc[j];
+        acc.x = fmaf(p, v.x, acc.x); acc.y = fmaf(p, v.y, acc.y); acc.z = fmaf(p, v.z, acc.z); acc.w = fmaf(p, v.w, acc.w);
+      }
+    }
+    *reinterpret_cast<float4*>(&part[slice][d4 * 4]) = acc;
   }
-  for (; j < len; j += 4) o0 = fmaf(sc[j], __ldg(vp + size_t(j) * a.kv_ld), o0);
-  part[slice][dcol] = (o0 + o1) + (o2 + o3);
   __syncthreads();
-  if (tid < 64) a.out[size_t(b) * a.ldo + h * 64 + tid] = ((part[0][tid] + part[1][tid]) + (part[2][tid] + part[3][tid])) / sum;
+  if (tid < 64) {
+    float o = 0.0f;
+#pragma unroll
+    for (int s2 = 0; s2 < 16; ++s2) o += part[s2][tid];
+    loc[tid] = o;
+  }
+  if (tid == 0) { loc[64] = mx; loc[65] = sum; }
+  cluster.sync();
+  if (rank == 0 && tid < 64) {
+    float m = -INFINITY;
+    for (int r = 0; r < kDaSplit; ++r) m = fmaxf(m, cluster.map_shared_rank(loc, r)[64]);
+    float tot = 0.0f, o = 0.0f;
+    for (int r = 0; r < kDaSplit; ++r) {
+      const float* rl = cluster.map_shared_rank(loc, r);
+      const float wgt = expf(rl[64] - m);        // 0 for an empty slice (max = -inf, sum = 0)
+      tot = fmaf(rl[65], wgt, tot);
+      o = fmaf(rl[tid], wgt, o);
+    }
+    a.out[size_t(b) * a.ldo + h * 64 + tid] = o / tot;
+  }
+  cluster.sync();          // peers keep their shared memory until rank 0 has merged
 }
 
 int launch_decode_attention(const DecodeAttArgs& a, int batch, int heads, int max_len, cudaStream_t s) {
   if (batch <= 0 || heads <= 0) return YOHO_OK;
   if (batch > 65535) return fail(YOHO_ERR_UNSUPPORTED, "decode attention: batch=%d", batch);
-  const size_t smem = size_t(max_len) * sizeof(float);
-  if (smem > 200 * 1024) return fail(YOHO_ERR_UNSUPPORTED, "decode attention: %d cache rows exceed shared memory", max_len);
-  YOHO_CUDA_CHECK(cudaFuncSetAttribute(decode_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-  ProfScope prof(s, kProfOther, 4.0 * batch * heads * 64.0 * max_len);
-  decode_attention_kernel<<<dim3(heads, batch), kDaThreads, smem, s>>>(a);
+  if (max_len > kDaSplit * kDaLocal) return fail(YOHO_ERR_UNSUPPORTED, "decode attention: %d cache rows (<= %d)", max_len, kDaSplit * kDaLocal);
+  if (a.kv_ld % 4 != 0 || a.k_off % 4 != 0 || a.v_off % 4 != 0 || a.ldq % 4 != 0) return fail(YOHO_ERR_UNSUPPORTED, "decode attention: strides must be multiples of 4 floats");
+  ProfScope prof(s, kProfDecAttention, double(batch) * heads * max_len * 2.0 * 64 * sizeof(float));
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(heads, batch, kDaSplit);
+  cfg.blockDim = dim3(kDaThreads, 1, 1);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = kDaSplit;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  YOHO_CUDA_CHECK(cudaLaunchKernelEx(&cfg, decode_attention_kernel, a));
   YOHO_LAUNCH_CHECK("decode_attention_kernel");
   return YOHO_OK;
 }
