@@ -223,6 +223,8 @@ def main():
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # one process per GPU: keep each rank's threads and pinned staging buffers on the GPU's own NUMA node
+    host_cpus = yd.bind_host_to_gpu(local_rank) if world > 1 else []
     lib = _lib.load()
     pk = peaks()
 
@@ -357,7 +359,8 @@ def main():
         "dtype": "bf16" if "encoder" in stages else "f32", "data": "synthetic",
         "config": {"workload": desc, "model": model, "clips_per_gpu": clips, "global_clips": total_clips, "clip_seconds": CLIP_SECONDS,
                    "stages": stages, "norm": args.norm, "compute": "bf16 operands / fp32 accumulate (tcgen05); fp32 frontend, residual stream and LayerNorm",
-                   "parallelism": f"clips sharded over {world} GPU(s), no collective", "weights": "random-init (seed 42)",
+                   "parallelism": f"clips sharded over {world} GPU(s), no collective", "host_cpus_per_rank": len(host_cpus) or None,
+                   "weights": "random-init (seed 42)",
                    "l2": f"inputs larger than L2: {B * N_SAMPLES * 4 / 1e6:.0f} MB PCM per GPU per step, activations stream through HBM"},
         "e2e": {"value": round(e2e_value, 1), "unit": "x realtime", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": round(ms_e2e, 4), "chunk_clips": args.e2e_chunk},

@@ -43,6 +43,27 @@ def init_process_group(backend: str | None = None) -> tuple[int, int, int]:
     return rank, local_rank, world
 
 
+def bind_host_to_gpu(device_index: int) -> list[int]:
+    """Pin this process (and so its pinned staging buffers, first-touch) to the CPUs NVML reports as local to the GPU.
+    With one process per GPU every rank moves ~15 GB/s through host memory on the host-facing path; without the binding
+    half of that crosses the socket interconnect.  Returns the CPU list, or [] when NVML / affinity is unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        props = torch.cuda.get_device_properties(device_index)
+        bus = f"{props.pci_domain_id:08x}:{props.pci_bus_id:02x}:{props.pci_device_id:02x}.0"
+        handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        n_cpu = os.cpu_count() or 1
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, (n_cpu + 63) // 64)
+        cpus = [i for i in range(n_cpu) if (mask[i // 64] >> (i % 64)) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return []
+
+
 def barrier():
     if dist.is_initialized():
         dist.barrier()
