@@ -22,6 +22,7 @@ struct DecLayerOff {
   size_t ln2_s, ln2_b, w1, b1, w2, b2;
   // derived: fused [k | v] projections and their biases [0 | bv] (key_proj has no bias, whisper.py:33)
   size_t s_wkv, s_bkv, c_wkv, c_bkv;
+  size_t s_wqkv, s_bqkv;   // [q | k | v] and [bq | 0 | bv] for the one-launch self-attention projection of the cached step
 };
 struct DecBlob {
   size_t pos, emb, lnf_s, lnf_b;
@@ -73,6 +74,7 @@ static DecBlob dec_plan_blob(const yoho_decoder_desc& d) {
   for (auto& l : L.layers) {
     l.s_wkv = take(D * 2 * D * f); l.s_bkv = take(2 * D * f);
     l.c_wkv = take(A * 2 * D * f); l.c_bkv = take(2 * D * f);
+    l.s_wqkv = take(D * 3 * D * f); l.s_bqkv = take(3 * D * f);
   }
   L.total = align_up(off, 1024);
   return L;
@@ -94,6 +96,14 @@ __global__ void dec_pair_cols_kernel(const float* __restrict__ a, const float* _
     const int r = int(i / cols), c = int(i - (long long)r * cols);
     out[size_t(r) * 2 * cols + c] = a[i];
     out[size_t(r) * 2 * cols + cols + c] = b[i];
+  }
+}
+
+// dst (rows, ld) columns [c0, c0 + cols) <- src (rows, cols)
+__global__ void dec_place_cols_kernel(const float* __restrict__ src, float* __restrict__ dst, int rows, int cols, int ld, int c0) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (long long)rows * cols; i += (long long)gridDim.x * blockDim.x) {
+    const int r = int(i / cols), c = int(i - (long long)r * cols);
+    dst[size_t(r) * ld + c0 + c] = src[i];
   }
 }
 
@@ -151,17 +161,36 @@ static StepWs dec_plan_step_ws(const yoho_decoder_desc& d, int batch) {
   return w;
 }
 
-static int dec_skinny(const float* x, int ldx, int b0, int nb, int k, const float* w, int ldw, int n, const float* bias, float* out,
-                      long long out_row_stride, const int* row_off_ptr, int row_off_mul, int gelu, int acc, cudaStream_t s) {
-  SkinnyArgs a;
-  a.x = x + size_t(b0) * ldx; a.ldx = ldx; a.w = w; a.ldw = ldw; a.bias = bias;
-  a.out = out + (long long)b0 * out_row_stride; a.out_row_stride = out_row_stride;
-  a.row_off_ptr = row_off_ptr; a.row_off_mul = row_off_mul;
-  a.b = nb; a.k = k; a.n = n; a.gelu = gelu; a.accumulate = acc;
-  return launch_skinny_gemm(a, s);
+struct DenseOpt {
+  const float* bias = nullptr;
+  const float* ln_scale = nullptr; const float* ln_bias = nullptr;     // LayerNorm of the input rows, fused into the load
+  float* out2 = nullptr; long long out2_row_stride = 0; int n_split = 0;
+  const int* row_off_ptr = nullptr; int row_off_mul = 0;
+  int gelu = 0, accumulate = 0;
+};
+
+// out (batch rows) = act(LN?(x) @ w + bias); the skinny GEMM keeps <= 64 activation rows in registers, larger batches go
+// in slices (the weights then come from L2)
+static int dec_skinny(const float* x, int ldx, int batch, int k, const float* w, int ldw, int n, float* out, long long out_row_stride,
+                      const DenseOpt& o, cudaStream_t s) {
+  for (int b0 = 0; b0 < batch; b0 += 64) {
+    SkinnyArgs a;
+    a.x = x + size_t(b0) * ldx; a.ldx = ldx; a.w = w; a.ldw = ldw; a.bias = o.bias;
+    a.out = out + (long long)b0 * out_row_stride; a.out_row_stride = out_row_stride;
+    a.out2 = o.out2 ? o.out2 + (long long)b0 * o.out2_row_stride : nullptr; a.out2_row_stride = o.out2_row_stride; a.n_split = o.n_split;
+    a.row_off_ptr = o.row_off_ptr; a.row_off_mul = o.row_off_mul;
+    a.ln_scale = o.ln_scale; a.ln_bias = o.ln_bias;
+    a.b = batch - b0 < 64 ? batch - b0 : 64; a.k = k; a.n = n; a.gelu = o.gelu; a.accumulate = o.accumulate;
+    int r = launch_skinny_gemm(a, s);
+    if (r != YOHO_OK) return r;
+  }
+  return YOHO_OK;
 }
 
 // One token for every clip: consumes tokens[:, p], appends to the self cache at p, leaves logits for position p + 1.
+// 8 launches per layer: every LayerNorm is fused into the GEMM that consumes it (each CTA recomputes the statistics of
+// the few rows; from 17 rows on a separate LayerNorm launch is cheaper), q | k | v of the self attention is one GEMM whose
+// k | v columns land in the cache row of the current position.
 static int dec_step(const yoho_decoder_desc& d, const DecBlob& L, const char* blob, const DecCache& c, const int* tokens, int tok_ld,
                     int batch, char* ws, const StepWs& w, float* logits, int logits_ld, cudaStream_t s) {
   const int D = d.dims, H = d.n_heads, T = d.audio_len, S = d.seq_len;
@@ -171,51 +200,61 @@ static int dec_step(const yoho_decoder_desc& d, const DecBlob& L, const char* bl
   float* q = reinterpret_cast<float*>(ws + w.q);
   float* att = reinterpret_cast<float*>(ws + w.att);
   float* h = reinterpret_cast<float*>(ws + w.h);
-  YOHO_TRY(launch_embed(tokens, tok_ld, c.pos, batch, 1, F32(L.emb), F32(L.pos), x, D, d.vocab, s));
-  // the skinny GEMM keeps <= 64 activation rows in registers: larger batches go in slices (weights then come from L2)
-  auto dense = [&](const float* in, int ldx, int k, size_t w_off, int n, size_t b_off, bool has_bias, float* out, long long ors,
-                   const int* rop, int rom, int gelu, int acc) -> int {
-    for (int b0 = 0; b0 < batch; b0 += 64)
-      YOHO_TRY(dec_skinny(in, ldx, b0, batch - b0 < 64 ? batch - b0 : 64, k, F32(w_off), n, n, has_bias ? F32(b_off) : nullptr, out, ors,
-                          rop, rom, gelu, acc, s));
-    return YOHO_OK;
+  const bool fuse_ln = batch <= 16;
+  // input of a GEMM that consumes LN(x): x itself with the LayerNorm fused into the load, or a normalised copy
+  auto normed = [&](size_t scale, size_t bias, DenseOpt& o, const float** in) -> int {
+    if (fuse_ln) { o.ln_scale = F32(scale); o.ln_bias = F32(bias); *in = x; return YOHO_OK; }
+    *in = xn;
+    return launch_layernorm_f32(x, F32(scale), F32(bias), xn, batch, D, s);
   };
+  const float* in = nullptr;
+  YOHO_TRY(launch_embed(tokens, tok_ld, c.pos, batch, 1, F32(L.emb), F32(L.pos), x, D, d.vocab, s));
   for (int i = 0; i < d.n_layers; ++i) {
     const DecLayerOff& l = L.layers[i];
     float* self_kv = c.self_kv + c.self_layer * i;
     const float* cross_kv = c.cross_kv + c.cross_layer * i;
     // q += out_proj(attention(LN(q), cache))                         whisper.py:95-99
-    YOHO_TRY(launch_layernorm_f32(x, F32(l.ln0_s), F32(l.ln0_b), xn, batch, D, s));
-    YOHO_TRY(dense(xn, D, D, l.s_wq, D, l.s_bq, true, q, D, nullptr, 0, 0, 0));
-    YOHO_TRY(dense(xn, D, D, l.s_wkv, 2 * D, l.s_bkv, true, self_kv, (long long)S * 2 * D, c.pos, 2 * D, 0, 0));
+    {
+      DenseOpt o;
+      o.bias = F32(l.s_bqkv);
+      YOHO_TRY(normed(l.ln0_s, l.ln0_b, o, &in));
+      o.out2 = self_kv; o.out2_row_stride = (long long)S * 2 * D; o.n_split = D; o.row_off_ptr = c.pos; o.row_off_mul = 2 * D;
+      YOHO_TRY(dec_skinny(in, D, batch, D, F32(l.s_wqkv), 3 * D, 3 * D, q, D, o, s));
+    }
     {
       DecodeAttArgs a;
       a.q = q; a.ldq = D; a.kv = self_kv; a.kv_clip_stride = (long long)S * 2 * D; a.kv_ld = 2 * D; a.k_off = 0; a.v_off = D;
       a.len_ptr = c.pos; a.len_add = 1; a.out = att; a.ldo = D;
       YOHO_TRY(launch_decode_attention(a, batch, H, S, s));
     }
-    YOHO_TRY(dense(att, D, D, l.s_wo, D, l.s_bo, true, x, D, nullptr, 0, 0, 1));
+    { DenseOpt o; o.bias = F32(l.s_bo); o.accumulate = 1; YOHO_TRY(dec_skinny(att, D, batch, D, F32(l.s_wo), D, D, x, D, o, s)); }
     // x += out_proj(attention(LN(x), encoder states))                whisper.py:101-105
-    YOHO_TRY(launch_layernorm_f32(x, F32(l.ln1_s), F32(l.ln1_b), xn, batch, D, s));
-    YOHO_TRY(dense(xn, D, D, l.c_wq, D, l.c_bq, true, q, D, nullptr, 0, 0, 0));
+    {
+      DenseOpt o;
+      o.bias = F32(l.c_bq);
+      YOHO_TRY(normed(l.ln1_s, l.ln1_b, o, &in));
+      YOHO_TRY(dec_skinny(in, D, batch, D, F32(l.c_wq), D, D, q, D, o, s));
+    }
     {
       DecodeAttArgs a;
       a.q = q; a.ldq = D; a.kv = cross_kv; a.kv_clip_stride = (long long)T * 2 * D; a.kv_ld = 2 * D; a.k_off = 0; a.v_off = D;
       a.len_const = T; a.out = att; a.ldo = D;
       YOHO_TRY(launch_decode_attention(a, batch, H, T, s));
     }
-    YOHO_TRY(dense(att, D, D, l.c_wo, D, l.c_bo, true, x, D, nullptr, 0, 0, 1));
+    { DenseOpt o; o.bias = F32(l.c_bo); o.accumulate = 1; YOHO_TRY(dec_skinny(att, D, batch, D, F32(l.c_wo), D, D, x, D, o, s)); }
     // x += Dense_1(gelu(Dense_0(LN(x))))                             whisper.py:107-112
-    YOHO_TRY(launch_layernorm_f32(x, F32(l.ln2_s), F32(l.ln2_b), xn, batch, D, s));
-    YOHO_TRY(dense(xn, D, D, l.w1, 4 * D, l.b1, true, h, 4 * D, nullptr, 0, 1, 0));
-    YOHO_TRY(dense(h, 4 * D, 4 * D, l.w2, D, l.b2, true, x, D, nullptr, 0, 0, 1));
+    {
+      DenseOpt o;
+      o.bias = F32(l.b1); o.gelu = 1;
+      YOHO_TRY(normed(l.ln2_s, l.ln2_b, o, &in));
+      YOHO_TRY(dec_skinny(in, D, batch, D, F32(l.w1), 4 * D, 4 * D, h, 4 * D, o, s));
+    }
+    { DenseOpt o; o.bias = F32(l.b2); o.accumulate = 1; YOHO_TRY(dec_skinny(h, 4 * D, batch, 4 * D, F32(l.w2), D, D, x, D, o, s)); }
   }
-  YOHO_TRY(launch_layernorm_f32(x, F32(L.lnf_s), F32(L.lnf_b), xn, batch, D, s));
-  // logits = x @ embedding.T                                        whisper.py:163
-  for (int b0 = 0; b0 < batch; b0 += 64)
-    YOHO_TRY(dec_skinny(xn, D, b0, batch - b0 < 64 ? batch - b0 : 64, D, F32(L.emb_t), vocab_ld(d), d.vocab, nullptr, logits, logits_ld,
-                        nullptr, 0, 0, 0, s));
-  return YOHO_OK;
+  // logits = LN(x) @ embedding.T                                    whisper.py:162-163
+  DenseOpt o;
+  YOHO_TRY(normed(L.lnf_s, L.lnf_b, o, &in));
+  return dec_skinny(in, D, batch, D, F32(L.emb_t), vocab_ld(d), d.vocab, logits, logits_ld, o, s);
 }
 
 // ------------------------------------------------------------------------------ teacher-forced forward (float32)
@@ -343,6 +382,13 @@ extern "C" int yoho_decoder_weights_pack(yoho_ctx* ctx, const yoho_decoder_desc*
     YOHO_LAUNCH_CHECK("dec_pair_cols_kernel");
     dec_pair_cols_kernel<<<ceil_div(A * D, 256), 256, 0, s>>>(F32(l.c_wk), F32(l.c_wv), F32(l.c_wkv), A, D);
     YOHO_LAUNCH_CHECK("dec_pair_cols_kernel");
+    dec_place_cols_kernel<<<ceil_div(D * D, 256), 256, 0, s>>>(F32(l.s_wq), F32(l.s_wqkv), D, D, 3 * D, 0);
+    YOHO_LAUNCH_CHECK("dec_place_cols_kernel");
+    dec_place_cols_kernel<<<ceil_div(D * 2 * D, 256), 256, 0, s>>>(F32(l.s_wkv), F32(l.s_wqkv), D, 2 * D, 3 * D, D);
+    YOHO_LAUNCH_CHECK("dec_place_cols_kernel");
+    YOHO_TRY(launch_fill_zero(blob + l.s_bqkv, size_t(3) * D * sizeof(float), s));
+    YOHO_CUDA_CHECK(cudaMemcpyAsync(blob + l.s_bqkv, blob + l.s_bq, D * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    YOHO_CUDA_CHECK(cudaMemcpyAsync(blob + l.s_bqkv + size_t(2) * D * sizeof(float), blob + l.s_bv, D * sizeof(float), cudaMemcpyDeviceToDevice, s));
     for (size_t pair : {l.s_bkv, l.c_bkv}) YOHO_TRY(launch_fill_zero(blob + pair, size_t(2) * D * sizeof(float), s));
     YOHO_CUDA_CHECK(cudaMemcpyAsync(blob + l.s_bkv + size_t(D) * sizeof(float), blob + l.s_bv, D * sizeof(float), cudaMemcpyDeviceToDevice, s));
     YOHO_CUDA_CHECK(cudaMemcpyAsync(blob + l.c_bkv + size_t(D) * sizeof(float), blob + l.c_bv, D * sizeof(float), cudaMemcpyDeviceToDevice, s));
@@ -437,7 +483,6 @@ static int dec_step_checked(yoho_ctx* ctx, const yoho_decoder_desc* desc, const 
   for (int i = 0; i < n_steps; ++i) {
     YOHO_TRY(dec_step(*desc, L, static_cast<const char*>(blob), c, tokens, desc->seq_len, batch, static_cast<char*>(ws), w, lg, lg_ld, s));
     YOHO_TRY(launch_greedy_pick(lg, lg_ld, desc->vocab, tokens, desc->seq_len, desc->seq_len, batch, c.pos, forced, eot, s));
-    YOHO_TRY(launch_advance(c.pos, desc->seq_len, s));
   }
   return YOHO_OK;
 }
@@ -461,7 +506,7 @@ extern "C" int yoho_decoder_generate(yoho_ctx* ctx, const yoho_decoder_desc* des
 extern "C" int yoho_test_skinny_gemm(yoho_ctx* ctx, const float* x, const float* w, const float* bias, float* out, int b, int k, int n,
                                      int gelu, int accumulate, yoho_stream_t stream_) {
   if (!ctx || !x || !w || !out) return fail(YOHO_ERR_INVALID, "yoho_test_skinny_gemm: null argument");
-  for (int b0 = 0; b0 < b; b0 += 64)
-    YOHO_TRY(dec_skinny(x, k, b0, b - b0 < 64 ? b - b0 : 64, k, w, n, n, bias, out, n, nullptr, 0, gelu, accumulate, static_cast<cudaStream_t>(stream_)));
-  return YOHO_OK;
+  DenseOpt o;
+  o.bias = bias; o.gelu = gelu; o.accumulate = accumulate;
+  return dec_skinny(x, k, b, k, w, n, n, out, n, o, static_cast<cudaStream_t>(stream_));
 }

@@ -68,6 +68,35 @@ skinny_gemm_kernel(const SkinnyArgs a) {
 #pragma unroll
   for (int b = 0; b < BT; ++b) acc[b] = 0.0f;
 
+  // the first eight weight rows of every warp do not depend on the activations: pull their lines towards the SM before
+  // the LayerNorm statistics and the activation staging (a step is a chain of such latencies, not bandwidth)
+  {
+    const int len0 = min(kSkChunk, k_end - k_begin);
+    const float* wp0 = a.w + size_t(k_begin) * a.ldw + col;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int kk = warp + u * kSkWarps;
+      if (col_ok && kk < len0) asm volatile("prefetch.global.L1 [%0];" ::"l"(wp0 + size_t(kk) * a.ldw));
+    }
+  }
+
+  // fused LayerNorm: every CTA recomputes the statistics of the (few) activation rows over the full k
+  __shared__ float ln_mean[BT], ln_rstd[BT];
+  if (a.ln_scale) {
+    for (int b = warp; b < a.b; b += kSkWarps) {
+      const float* row = a.x + size_t(b) * a.ldx;
+      float s1 = 0.0f, s2 = 0.0f;
+      for (int k = lane; k < a.k; k += 32) { const float v = __ldg(row + k); s1 += v; s2 = fmaf(v, v, s2); }
+#pragma unroll
+      for (int o = 16; o; o >>= 1) { s1 += __shfl_xor_sync(0xffffffffu, s1, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o); }
+      if (lane == 0) {
+        const float mean = s1 / a.k;
+        ln_mean[b] = mean;
+        ln_rstd[b] = rsqrtf(fmaxf(s2 / a.k - mean * mean, 0.0f) + 1e-6f);
+      }
+    }
+  }
+
   for (int k0 = k_begin; k0 < k_end; k0 += kSkChunk) {
     const int len = min(kSkChunk, k_end - k0);
     __syncthreads();
@@ -75,7 +104,11 @@ skinny_gemm_kernel(const SkinnyArgs a) {
     const int len_pad = min(kSkChunk, (len + 8 * kSkWarps - 1) / (8 * kSkWarps) * (8 * kSkWarps));
     for (int idx = tid; idx < BT * len_pad; idx += kSkThreads) {
       const int b = idx / len_pad, kk = idx - b * len_pad;
-      const float v = (b < a.b && kk < len) ? __ldg(a.x + size_t(b) * a.ldx + k0 + kk) : 0.0f;
+      float v = 0.0f;
+      if (b < a.b && kk < len) {
+        v = __ldg(a.x + size_t(b) * a.ldx + k0 + kk);
+        if (a.ln_scale) v = fmaf((v - ln_mean[b]) * ln_rstd[b], __ldg(a.ln_scale + k0 + kk), __ldg(a.ln_bias + k0 + kk));
+      }
       xs[kk * BT + (((b >> 2) ^ (kk & (G - 1))) << 2) + (b & 3)] = v;
     }
     __syncthreads();
@@ -133,7 +166,10 @@ skinny_gemm_kernel(const SkinnyArgs a) {
     if (b >= a.b || c >= a.n) continue;
     if (a.bias) v += __ldg(a.bias + c);
     if (a.gelu) v = dec_gelu_tanh(v);
-    float* dst = a.out + (long long)b * a.out_row_stride + row_off + c;
+    float* dst;
+    if (a.n_split > 0) dst = c < a.n_split ? a.out + (long long)b * a.out_row_stride + c
+                                           : a.out2 + (long long)b * a.out2_row_stride + row_off + (c - a.n_split);
+    else dst = a.out + (long long)b * a.out_row_stride + row_off + c;
     *dst = a.accumulate ? *dst + v : v;
   }
   if (KS > 1) cg::this_cluster().sync();          // peers keep their shared memory until everyone has read it
@@ -159,7 +195,10 @@ static int skinny_launch(const SkinnyArgs& a, cudaStream_t s) {
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = KS; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  // No cluster attribute for the variant without a k split: launched as 1 x 1 x 1 clusters, two of those instantiations
+  // computed their shared-memory addresses from SR_CgaCtaId and faulted ("operation not supported on global/shared
+  // address space") or returned garbage; as plain launches all of them pass.
+  cfg.numAttrs = KS > 1 ? 1 : 0;
   YOHO_CUDA_CHECK(cudaLaunchKernelEx(&cfg, skinny_gemm_kernel<BT, KS>, a));
   YOHO_LAUNCH_CHECK("skinny_gemm_kernel");
   return YOHO_OK;
@@ -174,9 +213,7 @@ int launch_skinny_gemm(const SkinnyArgs& a, cudaStream_t s) {
 #define YOHO_SK(BT)                                                          \
   return wide ? skinny_launch<BT, 1>(a, s) : skinny_launch<BT, 8>(a, s)
   if (a.b <= 4) { YOHO_SK(4); }
-  // the <8, 1> instantiation faults on the device ("operation not supported on global/shared address space") although
-  // its SASS reads like the other nine; 5..8 rows without a k split take the 16-row variant instead
-  if (a.b <= 8 && !wide) return skinny_launch<8, 8>(a, s);
+  if (a.b <= 8) { YOHO_SK(8); }
   if (a.b <= 16) { YOHO_SK(16); }
   if (a.b <= 32) { YOHO_SK(32); }
   YOHO_SK(64);
@@ -312,53 +349,54 @@ int launch_decode_attention(const DecodeAttArgs& a, int batch, int heads, int ma
 }
 
 // ---- greedy choice: tokens[b, p + 1] = argmax_v logits[b, v] unless that position is forced ---------------------------
-// First maximum wins (jnp.argmax, whisper.py:279).  A sequence that has produced `eot` keeps producing it.
+// First maximum wins (jnp.argmax, whisper.py:279).  A sequence that has produced `eot` keeps producing it.  The last CTA
+// to finish advances the position; the counter saturates at the last slot of the token buffer, so a step past the end
+// rewrites that slot instead of running off the caches.
 __global__ void __launch_bounds__(256)
 greedy_pick_kernel(const float* __restrict__ logits, int ld, int vocab, int* __restrict__ tokens, int tok_ld, int max_len,
-                   const int* __restrict__ pos_ptr, const unsigned char* __restrict__ forced, int eot) {
+                   int* __restrict__ pos_ptr, const unsigned char* __restrict__ forced, int eot) {
   __shared__ float bv[8];
   __shared__ int bi[8];
   const int b = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int p = *pos_ptr;
-  if (p + 1 >= max_len || (forced && forced[p + 1])) return;
-  const float* row = logits + size_t(b) * ld;
+  const int p = pos_ptr[0];
+  const bool write = p + 1 < max_len && !(forced && forced[p + 1]);
   float best = -INFINITY;
   int idx = 0x7fffffff;
-  for (int v = tid; v < vocab; v += 256) {
-    const float x = row[v];
-    if (x > best) { best = x; idx = v; }
-  }
+  if (write) {
+    const float* row = logits + size_t(b) * ld;
+    for (int v = tid; v < vocab; v += 256) {
+      const float x = row[v];
+      if (x > best) { best = x; idx = v; }
+    }
 #pragma unroll
-  for (int o = 16; o; o >>= 1) {
-    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
-    const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
-    if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
+    for (int o = 16; o; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+      if (ob > best || (ob == best && oi < idx)) { best = ob; idx = oi; }
+    }
+    if (lane == 0) { bv[warp] = best; bi[warp] = idx; }
   }
-  if (lane == 0) { bv[warp] = best; bi[warp] = idx; }
   __syncthreads();
   if (tid == 0) {
-    for (int w = 1; w < 8; ++w)
-      if (bv[w] > best || (bv[w] == best && bi[w] < idx)) { best = bv[w]; idx = bi[w]; }
-    int* t = tokens + size_t(b) * tok_ld;
-    t[p + 1] = (eot >= 0 && t[p] == eot) ? eot : idx;
+    if (write) {
+      for (int w = 1; w < 8; ++w)
+        if (bv[w] > best || (bv[w] == best && bi[w] < idx)) { best = bv[w]; idx = bi[w]; }
+      int* t = tokens + size_t(b) * tok_ld;
+      t[p + 1] = (eot >= 0 && t[p] == eot) ? eot : idx;
+    }
+    __threadfence();
+    if (atomicAdd(pos_ptr + 1, 1) == int(gridDim.x) - 1) {      // every CTA has read p by the time the last one gets here
+      pos_ptr[1] = 0;
+      pos_ptr[0] = min(p + 1, max_len - 1);
+    }
   }
 }
-
-// the counter saturates at the last slot of the token buffer, so a step past the end rewrites that slot instead of
-// running off the caches
-__global__ void advance_kernel(int* pos_ptr, int max_len) { *pos_ptr = min(*pos_ptr + 1, max_len - 1); }
 
 int launch_greedy_pick(const float* logits, int ld, int vocab, int* tokens, int tok_ld, int max_len, int batch, int* pos_ptr,
                        const unsigned char* forced, int eot, cudaStream_t s) {
   if (batch <= 0) return YOHO_OK;
   greedy_pick_kernel<<<batch, 256, 0, s>>>(logits, ld, vocab, tokens, tok_ld, max_len, pos_ptr, forced, eot);
   YOHO_LAUNCH_CHECK("greedy_pick_kernel");
-  return YOHO_OK;
-}
-
-int launch_advance(int* pos_ptr, int max_len, cudaStream_t s) {
-  advance_kernel<<<1, 1, 0, s>>>(pos_ptr, max_len);
-  YOHO_LAUNCH_CHECK("advance_kernel");
   return YOHO_OK;
 }
 

@@ -63,7 +63,11 @@ struct SkinnyArgs {
   const float* w = nullptr; int ldw = 0;            // (k, n) row-major weights (the Flax kernel layout)
   const float* bias = nullptr;                      // (n) or null
   float* out = nullptr; long long out_row_stride = 0;
-  const int* row_off_ptr = nullptr; int row_off_mul = 0;   // out += *row_off_ptr * row_off_mul (append at the device-side position)
+  const int* row_off_ptr = nullptr; int row_off_mul = 0;   // + *row_off_ptr * row_off_mul elements (append at the device-side position)
+  // optional second destination: columns >= n_split go to out2 (column c - n_split); the row offset then applies to out2
+  float* out2 = nullptr; long long out2_row_stride = 0; int n_split = 0;
+  // optional LayerNorm of the activation rows on load (flax: eps 1e-6, var = E[x^2] - E[x]^2 >= 0): scale / bias are (k)
+  const float* ln_scale = nullptr; const float* ln_bias = nullptr;
   int b = 0, k = 0, n = 0;
   int gelu = 0, accumulate = 0;
 };
@@ -75,9 +79,9 @@ struct DecodeAttArgs {
   float* out = nullptr; int ldo = 0;
 };
 int launch_decode_attention(const DecodeAttArgs& a, int batch, int heads, int max_len, cudaStream_t s);
+// pos_ptr[0] is the position, pos_ptr[1] a ticket counter: the last CTA to finish advances the position (saturating)
 int launch_greedy_pick(const float* logits, int ld, int vocab, int* tokens, int tok_ld, int max_len, int batch, int* pos_ptr,
                        const unsigned char* forced, int eot, cudaStream_t s);
-int launch_advance(int* pos_ptr, int max_len, cudaStream_t s);
 
 // ---------------------------------------------------------------- gemm_sm100.cu (tcgen05)
 struct TapSpec { int col_off; int row_off; };
