@@ -128,3 +128,29 @@ def test_skinny_gemm(rt, b, k, n, gelu, acc):
     got = out.cpu().numpy()
     assert np.isfinite(got).all()
     assert np.abs(got - want).max() <= 2e-5 * max(1.0, np.abs(want).max())
+
+
+def test_transcriber_end_to_end(rt):
+    """PCM -> log-mel -> encoder -> KV-cached greedy decode through yoho_b200.pipeline.Transcriber (fp32 compute, so that
+    the token choice is comparable) equals the oracle chain: frontend -> audio_encoder -> full decoder re-run per token."""
+    from oracle import decoder as od, encoder as oe, frontend as ofe
+    from yoho_b200.nn import init_decoder_params, init_encoder_params
+    from yoho_b200.pipeline import Transcriber
+    from yoho_b200.synth import synth_batch
+    n_samples, B, D, H, V, L_MAX, n_new = 16000, 2, 128, 2, 300, 16, 8
+    params = {"audio_encoder": init_encoder_params(80, D, 2, seed=2), "text_decoder": init_decoder_params(V, L_MAX, D, 2, seed=3)}
+    pcm = synth_batch(B, n_samples, unique=B)
+    tr = Transcriber((80, D, H, 2), params, text_heads=H, text_seq_len=L_MAX, n_samples=n_samples, compute="fp32")
+    prompt = {0: 7, 2: 11, 3: 13}
+    got = tr.transcribe(pcm, prompt, max_new_tokens=n_new)
+    assert got.shape == (B, L_MAX)
+    mel = ofe.normalize_spectogram(ofe.mel_spectogram(pcm.astype(np.float64), 400, 160, 16000, 80))
+    states = oe.audio_encoder(params["audio_encoder"], mel, H, np.float64)
+    buf = np.zeros((B, L_MAX), np.int64)
+    forced = np.zeros(L_MAX, bool)
+    for pos, tok in prompt.items():
+        buf[:, pos], forced[pos] = tok, True
+    want = od.greedy_decode(params["text_decoder"], states, H, buf, forced, n_new)
+    assert np.array_equal(got, want)
+    on_dev = tr.transcribe(__import__("torch").from_numpy(pcm).cuda(), prompt, max_new_tokens=n_new, use_graph=True)
+    assert np.array_equal(on_dev.cpu().numpy(), want)

@@ -1,6 +1,7 @@
 """End-to-end clip pipeline: PCM -> log-mel -> Whisper audio encoder, the composition the reference
 runs at transcription_pretrain_no_voiceprints.py:172-179 + :198-203 and whisper.py:255-258
-(``mel_spectogram`` -> ``normalize_spectogram`` -> ``model.apply(..., method=Whisper.encode_audio)``).
+(``mel_spectogram`` -> ``normalize_spectogram`` -> ``model.apply(..., method=Whisper.encode_audio)``), and
+``Transcriber``: the same followed by the greedy token loop of whisper.py:260-285 on the KV-cached decoder.
 
 ``ClipEncoder.encode`` keeps everything in HBM (device tensors in, device tensor out).
 ``ClipEncoder.encode_host`` is the host-facing call: pinned host PCM in, pinned host encoder states
@@ -193,3 +194,40 @@ class ClipEncoder:
             if sync:
                 drained[-1].synchronize()
         return out_host
+
+
+class Transcriber:
+    """PCM clips -> token ids: the reference's demo (whisper.py:249-285) for a batch, everything on the device.
+
+    ``params`` is the reference's Whisper pytree ``{"audio_encoder": ..., "text_decoder": ...}`` (optionally under
+    ``"params"``); ``model`` names the encoder shape, the decoder shape is read from the pytree.  The prompt layout is
+    the caller's: ``prompt`` maps positions to forced token ids (the reference sets 0 -> <|startoftranscript|>,
+    2 -> <|transcribe|>, 3 -> <|notimestamps|> and lets the model choose position 1, the language, :266-272)."""
+
+    def __init__(self, model, params: dict, text_heads: int, text_seq_len: int = 448, n_samples: int = 480000, norm: str = "reference",
+                 compute: str = "bf16", device: int | None = None):
+        from .nn.whisper import TextDecoder
+        params = params.get("params", params)
+        self.encoder = ClipEncoder(model, params["audio_encoder"], n_samples=n_samples, norm=norm, compute=compute, device=device)
+        self.dec_params = params["text_decoder"]
+        vocab, dims = np.shape(self.dec_params["Embed_0"]["embedding"])
+        n_layers = sum(1 for k in self.dec_params if k.startswith("DecoderBlock_"))
+        self.decoder = TextDecoder(vocab_size=int(vocab), seq_len=text_seq_len, dims=int(dims), n_heads=text_heads, n_layers=n_layers)
+
+    def transcribe(self, pcm, prompt: dict[int, int], max_new_tokens: int | None = None, eot: int = -1, use_graph: bool = False):
+        """pcm (B, n_samples) float32 / int16 (host or CUDA) -> tokens (B, text_seq_len) int32 (same residency)."""
+        rt = self.encoder.rt
+        host = not (isinstance(pcm, torch.Tensor) and pcm.is_cuda)
+        is16 = (pcm.dtype == torch.int16) if isinstance(pcm, torch.Tensor) else (np.asarray(pcm).dtype == np.int16)
+        dev_pcm = rt.to_device(pcm, "pcm", torch.int16 if is16 else torch.float32)
+        with torch.cuda.device(rt.device):
+            states = self.encoder.encode(dev_pcm)
+        L = self.decoder.seq_len
+        tokens = torch.zeros((dev_pcm.shape[0], L), dtype=torch.int32, device=rt.device)
+        forced = np.zeros(L, np.uint8)
+        for pos, tok in prompt.items():
+            tokens[:, pos] = int(tok)
+            forced[pos] = 1
+        n_steps = L - 1 if max_new_tokens is None else min(L - 1, int(max_new_tokens))
+        out = self.decoder.generate({"params": self.dec_params}, states, tokens, forced=forced, n_steps=n_steps, eot=eot, use_graph=use_graph)
+        return out.cpu().numpy() if host else out
