@@ -207,3 +207,35 @@ def test_encode_host_matches_device_path(rt, pcm_dtype):
     f32 = pcm[:2].astype(np.float32) / 32768.0 if pcm_dtype == "int16" else pcm[:2]
     want = ofe.normalize_spectogram(ofe.mel_spectogram(f32.astype(np.float64), 400, 160, 16000, 80))
     assert np.abs(mel - want).max() <= 1e-4
+
+
+def test_encoder_properties_at_bench_size(rt):
+    """BASELINE configs[2] per-GPU shard (whisper-small, 256 x 30 s clips), where the float64 oracle is out of reach:
+    size-independent properties of the path.  A clip's states do not depend on its position in the batch or on its
+    neighbours (clips 128..255 repeat clips 0..127; one clip alone == its slot in the batch), two runs are bit-identical
+    (no atomics, no split-k on the data path), every value is finite, and the tcgen05 path agrees with the float32 SIMT
+    path (itself checked against the oracle at the sizes above) within the bf16 tolerance."""
+    import torch
+    from yoho_b200 import MODEL_SHAPES
+    from yoho_b200.nn import init_encoder_params
+    from yoho_b200.pipeline import ClipEncoder
+    from yoho_b200.synth import synth_batch
+    n_mels, dims, heads, layers = MODEL_SHAPES["small"]
+    params = init_encoder_params(n_mels, dims, layers, seed=42)
+    enc = ClipEncoder("small", params)
+    half = synth_batch(128, 480000, unique=128)
+    pcm = torch.from_numpy(np.concatenate([half, half])).cuda()
+    out = enc.encode(pcm)
+    assert out.shape == (256, 1500, dims) and bool(torch.isfinite(out).all())
+    assert torch.equal(out[:128], out[128:])
+    again = enc.encode(pcm)
+    assert torch.equal(out, again)
+    alone = enc.encode(pcm[37:38].contiguous())
+    assert torch.equal(alone[0], out[37])
+    chunked = enc.encode(pcm, chunk_clips=48)                  # 48-clip kernel sequences: same tiles per clip
+    assert torch.equal(chunked, out)
+    enc32 = ClipEncoder("small", params, compute="fp32")
+    ref = enc32.encode(pcm[:2].contiguous())
+    assert float((out[:2] - ref).abs().max() / ref.abs().max()) <= TOL_BF16
+    # distinct clips give distinct states (the batch is not collapsing onto one clip)
+    assert float((out[0] - out[1]).abs().max()) > 1e-3
