@@ -79,8 +79,10 @@ int yoho_stft_frames(int n_samples, int n_fft, int hop);
 /* Replaces mel_filter_banks(sr, n_fft, n_mels) as a *device constant*
  * (mel_filterbanks.py:21-42, consumed at audio.py:35-36).  `host_filters` is the dense
  * row-major (n_mels, n_bins) float32 matrix on the HOST; it is packed into per-row
- * bands [lo, hi) covering every non-zero and uploaded.  Setup call: may allocate and
- * synchronise. */
+ * bands [lo, hi) covering every non-zero, sorted longest first into the round schedule
+ * the log-mel kernel's ten warps walk, and uploaded.  Limits (YOHO_ERR_UNSUPPORTED
+ * beyond them): n_mels <= 160, n_bins <= 204, n_mels x (longest band rounded up to 4)
+ * <= 3072 weights.  Setup call: may allocate and synchronise. */
 int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, int n_mels, int n_bins,
                            yoho_filterbank** out);
 int yoho_filterbank_destroy(yoho_filterbank* fb);
