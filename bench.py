@@ -363,7 +363,7 @@ def main():
                    "weights": "random-init (seed 42)",
                    "l2": f"inputs larger than L2: {B * N_SAMPLES * 4 / 1e6:.0f} MB PCM per GPU per step, activations stream through HBM"},
         "e2e": {"value": round(e2e_value, 1), "unit": "x realtime", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": round(ms_e2e, 4), "chunk_clips": args.e2e_chunk},
+                "ms_per_step": round(ms_e2e, 4), "chunk_clips": getattr(enc, "last_chunk_clips", args.e2e_chunk)},
         "gpu_launches": int(launches),
         "roofline": roofline, "rooflines": rooflines,
         "tflops_encoder": round(total_clips * GFLOP_PER_CLIP[model] / ms_step / world, 2) if "encoder" in stages else None,

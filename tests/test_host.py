@@ -113,7 +113,7 @@ def test_shard_range_partitions():
 
 def test_chunk_plan_partitions_the_batch():
     """The host pipeline's chunk plan (yoho_b200.pipeline.chunk_plan) covers every clip once, in order, never
-    exceeds the staging size, and tapers only when the batch has four chunks to spare."""
+    exceeds the staging size, and tapers only when the batch holds at least two chunks."""
     from yoho_b200.pipeline import chunk_plan
     for batch in (1, 7, 32, 127, 128, 130, 256, 1000):
         for chunk in (1, 2, 5, 32, 64):
@@ -123,4 +123,5 @@ def test_chunk_plan_partitions_the_batch():
                 assert all(0 < n <= chunk for _, n in plan)
                 assert all(plan[i][0] + plan[i][1] == plan[i + 1][0] for i in range(len(plan) - 1))
     assert [n for _, n in chunk_plan(256, 32)] == [8, 24, 32, 32, 32, 32, 32, 32, 16, 8, 8]
-    assert [n for _, n in chunk_plan(64, 32)] == [32, 32]
+    assert [n for _, n in chunk_plan(64, 32)] == [8, 24, 16, 8, 8]
+    assert [n for _, n in chunk_plan(48, 32, taper=True)] == [32, 16]

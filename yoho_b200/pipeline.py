@@ -28,10 +28,10 @@ _COMPUTE = {"bf16": COMPUTE_BF16, "fp32": COMPUTE_FP32}
 def chunk_plan(batch: int, chunk: int, taper: bool = True) -> list[tuple[int, int]]:
     """[(first clip, clips)] of the pipelined host path.  The copies of all but the first chunk's input and
     the last chunk's output hide behind kernels, so with ``taper`` the first chunk is a quarter and the last
-    two are a half and a quarter of ``chunk`` (when the batch has at least four chunks to spare)."""
+    three are a half and two quarters of ``chunk`` (when the batch holds at least two chunks)."""
     sizes: list[int] = []
     q = chunk // 4
-    if taper and q >= 1 and batch >= 4 * chunk:
+    if taper and q >= 1 and batch >= 2 * chunk:
         head, tail = [q, chunk - q], [chunk // 2, chunk - chunk // 2 - q, q]
         body = batch - 2 * chunk
         sizes = head + [chunk] * (body // chunk) + ([body % chunk] if body % chunk else []) + tail
@@ -146,7 +146,8 @@ class ClipEncoder:
         if out_host is None:
             out_host = torch.empty((B, self.seq_len, self.dims), dtype=torch.float32, pin_memory=True)
         dev = self.rt.device
-        chunk = max(1, min(int(chunk_clips), B))
+        chunk = max(1, min(int(chunk_clips), (B + 1) // 2))     # at least two chunks, so that copies can hide behind kernels
+        self.last_chunk_clips = chunk
         with torch.cuda.device(dev):
             if self._streams is None:
                 self._streams = tuple(torch.cuda.Stream(device=dev) for _ in range(3))
