@@ -310,6 +310,42 @@ def stage_attnperf():
               f"{us * 1e-6 * 1.9e9 * 148 / tiles:6.0f} SM-cycles@1.9GHz per 128x128 tile pair")
 
 
+def stage_attnphases():
+    """Debug build only (YOHO_EXTRA_NVCC_FLAGS=-DYOHO_ATT_TIMING): clock64 totals of the softmax phases of CTA 0 / warp 0."""
+    rt = get_runtime()
+    lib = rt.lib
+    raw = C.CDLL(str(_lib_path()))
+    batch, t, heads = 64, 1500, 12
+    qkv = torch.randn((batch, t, 3, heads, 64), device="cuda")
+    out = torch.empty((batch, t, heads * 64), device="cuda")
+    nbytes = lib.yoho_test_attention_workspace_bytes(batch, t, heads)
+    ws = rt.workspace("test", nbytes)
+    for _ in range(3):
+        check(lib.yoho_test_attention_bf16(rt.ctx, C.c_void_p(qkv.data_ptr()), C.c_void_p(out.data_ptr()), batch, t, heads,
+                                           C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
+    torch.cuda.synchronize()
+    ph16 = (C.c_longlong * 16)()
+    assert raw.yoho_debug_att_phases(ph16) == 0
+    ph = list(ph16)[:8]
+    names = ["loop top", "wait s_full", "tcgen05.ld x64 + wait", "row max + vote (+ rescale)", "scale, exp2, sum, pack", "tcgen05.st + wait + arrive",
+             "wait last P V (per item)", "O read-out + store (per item)"]
+    items = (batch * heads * ((t + 255) // 256) + 147) // 148
+    steps = items * ((t + 63) // 64)
+    total = sum(ph)
+    for n, v in zip(names, ph):
+        print(f"[attnphases] {n:32s} {v:10d} clk  {100.0 * v / total:5.1f} %   {v / steps:7.1f} clk/step")
+    mma_names = ["loop top", "wait p_full", "wait o_free / v_full", "issue P V (4 MMA + commits)", "[timing=2] wait P V complete", "issue Q K^T (g+2)",
+                 "[timing=2] wait Q K^T complete", "-"]
+    for n, v in zip(mma_names, list(ph16)[8:]):
+        print(f"[attnphases] MMA warp A: {n:32s} {v:10d} clk  {v / steps:7.1f} clk/step")
+    print(f"[attnphases] total {total} clk over {items} items / {steps} steps = {total / steps:.0f} clk/step (SFU floor 512 per warp, 1024 per sub-partition)")
+
+
+def _lib_path():
+    from yoho_b200 import build as b
+    return b.LIB
+
+
 if __name__ == "__main__":
     torch.cuda.init()
     print("device:", torch.cuda.get_device_name(0))

@@ -23,7 +23,7 @@ SOURCES = ["api.cu", "frontend.cu", "elementwise.cu", "encoder_fp32.cu", "gemm_s
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
-]
+] + os.environ.get("YOHO_EXTRA_NVCC_FLAGS", "").split()   # e.g. -DYOHO_ATT_TIMING for the phase-timing debug build
 
 
 def _nvcc() -> str:

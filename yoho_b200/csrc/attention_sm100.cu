@@ -54,7 +54,7 @@ struct AttParams {
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
@@ -62,6 +62,13 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
   asm("max.f32 %0, %1, %2, %3;" : "=f"(y) : "f"(a), "f"(b), "f"(c));
   return y;
 }
+
+#ifdef YOHO_ATT_TIMING
+__device__ long long g_att_phase[16];   // [0, 8) softmax warp 0, [8, 16) MMA warp of tile A; CTA 0
+#define ATT_T(i) do { long long now_ = clock64(); tacc[i] += now_ - tprev; tprev = now_; } while (0)
+#else
+#define ATT_T(i) do {} while (0)
+#endif
 
 __global__ void __launch_bounds__(kAttThreads, 1)
 attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, const AttParams p) {
@@ -159,13 +166,19 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
     };
     for (int g = 0; g < 2 && g < g_total; ++g) issue_qk(g);
     int p_it = 0, p_j = 0, p_st = 0; uint32_t p_ph = 0;
+#ifdef YOHO_ATT_TIMING
+    long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
+#endif
     for (int g = 0; g < g_total; ++g) {
       const int sb = g & 1, half = p_j & 1;
       const bool last = p_j == n_steps - 1;
+      ATT_T(0);
       mbar_wait(&sm.p_full[t][sb], (g >> 1) & 1);                        // P in TMEM, S consumed, O rescaled if needed
+      ATT_T(1);
       if (p_j == 0 && p_it > 0) mbar_wait(&sm.o_free[t], (p_it - 1) & 1);  // previous item's O has been read out
       mbar_wait(&sm.v_full[p_st], p_ph);
       tc_fence_after();
+      ATT_T(2);
       // A: 16 keys = 8 packed columns.  B: V rows are keys (128 B each): 16 keys = 2 groups of 8 rows, 1024 B apart
       const uint64_t bdesc = vdesc0 + uint64_t(p_st) * kStageDesc + uint64_t(half) * kHalfDesc;
       const uint32_t p_addr = s_tmem + uint32_t(sb * 64);
@@ -179,8 +192,22 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
         if (++p_st == kKvStages) { p_st = 0; p_ph ^= 1; }
       }
       if (last) { p_j = 0; ++p_it; } else { ++p_j; }
+      ATT_T(3);
+#if defined(YOHO_ATT_TIMING) && YOHO_ATT_TIMING >= 2
+      mbar_wait(&sm.o_full[t], g & 1);      // measurement only: P V chain latency (serialises the MMA warp)
+      ATT_T(4);
+#endif
       if (g + 2 < g_total) issue_qk(g + 2);
+      ATT_T(5);
+#if defined(YOHO_ATT_TIMING) && YOHO_ATT_TIMING >= 2
+      if (g + 2 < g_total) mbar_wait(&sm.s_full[t][sb], ((g + 2) >> 1) & 1);      // measurement only: Q K^T chain latency
+      ATT_T(6);
+#endif
     }
+#ifdef YOHO_ATT_TIMING
+    if (blockIdx.x == 0 && t == 0 && lane == 0)
+      for (int i = 0; i < 8; ++i) g_att_phase[8 + i] = tacc[i];
+#endif
     __syncwarp();
   } else {
     // ===================== softmax + output: warps 0-3 tile A, warps 4-7 tile B =====================
@@ -192,6 +219,9 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
     const float c = 0.125f * 1.4426950408889634f;            // d_head^-0.5 * log2(e)   (whisper.py:54-57)
     const int kv_tail = p.t_len - (n_steps - 1) * kStepKV;    // valid keys of the last step
     int g = 0;
+#ifdef YOHO_ATT_TIMING
+    long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
+#endif
     for (int it = 0; it < n_my; ++it) {
       const int item = int(blockIdx.x) + it * stride;
       const int qb = item % p.q_blocks, ch = item / p.q_blocks;
@@ -200,12 +230,15 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
       for (int j = 0; j < n_steps; ++j, ++g) {
         const int sb = g & 1;
         const uint32_t s_addr = s_base + uint32_t(sb * 64);
+        ATT_T(0);
         mbar_wait(&sm.s_full[t][sb], (g >> 1) & 1);
         tc_fence_after();
+        ATT_T(1);
         uint32_t a[32], b[32];
         tmem_ld_32x32b_x32(s_addr, a);
         tmem_ld_32x32b_x32(s_addr + 32, b);
         tmem_ld_wait();
+        ATT_T(2);
         if (j == n_steps - 1 && kv_tail < kStepKV) {          // CTA-uniform
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
@@ -243,32 +276,55 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
           }
           tmem_st_wait();
         }
-        const float mc = m_ref * c;
-        float l0 = 0.0f, l1 = 0.0f, l2 = 0.0f, l3 = 0.0f;
+        ATT_T(3);
+        // scale / shift and the row sum run on packed fp32 pairs (FFMA2 / FADD2: half the issue slots)
+        const uint64_t c2 = pack_f32x2(c, c), nmc2 = pack_f32x2(-m_ref * c, -m_ref * c);
+        uint64_t l01 = 0, l23 = 0;
         uint32_t packed[32];
+        // x[i] = key i (a) for i < 32, key i (b) beyond; exponentials are issued one block of kExpBlock ahead of their
+        // consumers so that the in-order warp never waits on a MUFU result with the SFU idle
+        float x[64];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          const float p0 = ex2_approx(fmaf(__uint_as_float(a[i]), c, -mc));
-          const float p1 = ex2_approx(fmaf(__uint_as_float(a[i + 1]), c, -mc));
-          const float r0 = ex2_approx(fmaf(__uint_as_float(b[i]), c, -mc));
-          const float r1 = ex2_approx(fmaf(__uint_as_float(b[i + 1]), c, -mc));
-          l0 += p0; l1 += p1; l2 += r0; l3 += r1;
-          __nv_bfloat162 u = __floats2bfloat162_rn(p0, p1), w = __floats2bfloat162_rn(r0, r1);
-          packed[i >> 1] = *reinterpret_cast<uint32_t*>(&u);          // keys i, i+1
-          packed[16 + (i >> 1)] = *reinterpret_cast<uint32_t*>(&w);   // keys 32 + i, i+1
+          unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(a[i]), __uint_as_float(a[i + 1])), c2, nmc2), x[i], x[i + 1]);
+          unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(b[i]), __uint_as_float(b[i + 1])), c2, nmc2), x[32 + i], x[33 + i]);
         }
-        l_run += (l0 + l1) + (l2 + l3);
+        constexpr int kExpBlock = 8;
+#pragma unroll
+        for (int i = 0; i < kExpBlock; ++i) x[i] = ex2_approx(x[i]);
+#pragma unroll
+        for (int blk = 0; blk < 64 / kExpBlock; ++blk) {
+          if (blk + 1 < 64 / kExpBlock) {
+#pragma unroll
+            for (int i = 0; i < kExpBlock; ++i) x[(blk + 1) * kExpBlock + i] = ex2_approx(x[(blk + 1) * kExpBlock + i]);
+          }
+#pragma unroll
+          for (int i = blk * kExpBlock; i < (blk + 1) * kExpBlock; i += 2) {
+            if (blk & 1) l23 = add_f32x2(l23, pack_f32x2(x[i], x[i + 1]));
+            else l01 = add_f32x2(l01, pack_f32x2(x[i], x[i + 1]));
+            __nv_bfloat162 u = __floats2bfloat162_rn(x[i], x[i + 1]);
+            packed[i >> 1] = *reinterpret_cast<uint32_t*>(&u);          // keys i, i+1
+          }
+        }
+        {
+          float l0, l1;
+          unpack_f32x2(add_f32x2(l01, l23), l0, l1);
+          l_run += l0 + l1;
+        }
+        ATT_T(4);
         tmem_st_32x32b_x32(s_addr, packed);      // P over the first 32 (already consumed) columns of this S buffer
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&sm.p_full[t][sb]);
+        ATT_T(5);
       }
       // last P V of the item: pull O into registers, hand O_t back to the MMA warp, then normalise and store.
       // (o_full cannot be used here: the softmax may be two P V commits ahead, and a parity wait only tells the
       // current phase from the previous one.  In the rescale path above s_full(g) implies P V(g-2) has retired.)
       mbar_wait(&sm.o_last[t], it & 1);
       tc_fence_after();
+      ATT_T(6);
       uint32_t o0[32], o1[32];
       tmem_ld_32x32b_x32(o_addr, o0);
       tmem_ld_32x32b_x32(o_addr + 32, o1);
@@ -295,7 +351,12 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
           *reinterpret_cast<uint4*>(dst + 32 + q4 * 8) = make_uint4(w1[0], w1[1], w1[2], w1[3]);
         }
       }
+      ATT_T(7);
     }
+#ifdef YOHO_ATT_TIMING
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+      for (int i = 0; i < 8; ++i) g_att_phase[i] = tacc[i];
+#endif
   }
 
   tc_fence_before();
@@ -328,3 +389,10 @@ int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16
 }
 
 }  // namespace yoho
+
+#ifdef YOHO_ATT_TIMING
+// debug builds only (-DYOHO_ATT_TIMING): clock64 totals of the softmax phases of CTA 0 / warp 0 of the last launch
+extern "C" int yoho_debug_att_phases(long long* out16) {
+  return int(cudaMemcpyFromSymbol(out16, yoho::g_att_phase, 16 * sizeof(long long)));
+}
+#endif
