@@ -334,16 +334,15 @@ def stage_attnphases():
     total = sum(ph)
     for n, v in zip(names, ph):
         print(f"[attnphases] {n:32s} {v:10d} clk  {100.0 * v / total:5.1f} %   {v / steps:7.1f} clk/step")
-    mma_names = ["loop top", "wait p_full", "wait o_free / v_full", "issue P V (4 MMA + commits)", "[timing=2] wait P V complete", "issue Q K^T (g+2)",
-                 "[timing=2] wait Q K^T complete", "-"]
+    mma_names = ["loop top", "wait p_full", "wait o_free / v_full", "issue P V (4 MMA + commits)", "-", "wait s_free + issue Q K^T (g+2)", "-", "-"]
     for n, v in zip(mma_names, list(ph16)[8:]):
         print(f"[attnphases] MMA warp A: {n:32s} {v:10d} clk  {v / steps:7.1f} clk/step")
     print(f"[attnphases] total {total} clk over {items} items / {steps} steps = {total / steps:.0f} clk/step (SFU floor 512 per warp, 1024 per sub-partition)")
 
 
 def _lib_path():
-    from yoho_b200 import build as b
-    return b.LIB
+    from yoho_b200 import _lib
+    return _lib.LIB_PATH
 
 
 if __name__ == "__main__":

@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kAttThreads, 1)
 attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, const AttParams p) {
   extern __shared__ __align__(1024) unsigned char att_smem_raw[];
   AttSmem& sm = *reinterpret_cast<AttSmem*>(att_smem_raw);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, int(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
     if (smem_u32(att_smem_raw) & 1023u) __trap();  // operand tiles need 1024-byte alignment (128B swizzle)
@@ -98,7 +98,7 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = sm.tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, sm.tmem_slot, 0);
   const int n_kv = p.n_kv, n_steps = p.n_steps;
   const int stride = int(gridDim.x);
   const int n_my = int(blockIdx.x) < p.n_items ? (p.n_items - int(blockIdx.x) + stride - 1) / stride : 0;   // items of this CTA
