@@ -117,7 +117,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle: ptxas then treats it (and everything in the role branches that derives from it) as
+  // warp-uniform, which keeps the producer's and the MMA issuer's loops on the uniform datapath
+  const int warp = __shfl_sync(0xffffffffu, int(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();          // 0 = leader (issues the MMAs)
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
 
@@ -138,7 +140,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   tc_fence_before();
   cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive / TMA signal
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   const int kblocks = p.n_taps * p.kblocks_per_tap;
 
@@ -171,6 +173,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (rank == 0) {
       // ===================== MMA issuer (leader CTA) =====================
       constexpr uint32_t idesc = make_idesc_bf16(kPairM, BN, 0, 0);
+      const uint64_t adesc0 = make_desc_sw128(smem_u32(stage_base), 16, 1024);
       int stage = 0; uint32_t phase = 0; int it = 0;
       for (int tile = cluster_id; tile < p.total_tiles; tile += n_clusters, ++it) {
         const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
@@ -180,17 +183,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          if (lane == 0) {
-            const uint32_t sa = smem_u32(stage_base + stage * Cfg::kStageBytes);
-            const uint64_t adesc = make_desc_sw128(sa, 16, 1024);
-            const uint64_t bdesc = make_desc_sw128(sa + Cfg::kABytes, 16, 1024);
+          // The warp stays converged and one elected lane issues (umma_*_w): a divergent `if (lane == 0)` block cost
+          // ~120 dependent instructions per k-block, more than the 512 tensor-pipe cycles its four MMAs take, and made
+          // this warp -- not the tensor pipe -- the limit (ncu: no wait on full_bar, pipe 70 % active).  The operand
+          // descriptors are linear in the stage index.
+          const uint64_t adesc = adesc0 + uint64_t(stage) * uint64_t(Cfg::kStageBytes >> 4);
+          const uint64_t bdesc = adesc + uint64_t(Cfg::kABytes >> 4);
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k)
-              umma_bf16_ss_2cta(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, (kb | k) != 0);
-            umma_commit_2cta_mcast(&empty_bar[stage], 0x3);          // both CTAs' smem slots reusable once these retire
-            if (kb == kblocks - 1) umma_commit_2cta_mcast(&tmem_full[as], 0x3);
-          }
-          __syncwarp();
+          for (int k = 0; k < kBlockK / 16; ++k)
+            umma_bf16_ss_2cta_w(d_tmem, adesc + uint64_t(k * 2), bdesc + uint64_t(k * 2), idesc, (kb | k) != 0);
+          umma_commit_2cta_mcast_w(&empty_bar[stage], 0x3);          // both CTAs' smem slots reusable once these retire
+          if (kb == kblocks - 1) umma_commit_2cta_mcast_w(&tmem_full[as], 0x3);
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
