@@ -17,6 +17,7 @@
 // the same S buffer (tcgen05.st) and keeps the row sum in registers.  O stays in TMEM across steps: it is
 // only rescaled when the running maximum grows by more than 2^8 (lazy rescaling; P is then bounded by 256), so
 // the common case has no correction.  Keys past the clip end are TMA zero-filled and masked to -inf.
+#include <cstdlib>
 #include "kernels.cuh"
 #include "ptx_sm100.cuh"
 
@@ -367,6 +368,12 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
 int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16* out, int batch, int t, int heads, cudaStream_t s) {
   if (!qkv || !out) return fail(YOHO_ERR_INVALID, "attention: null operand");
   if (batch <= 0 || t <= 0 || heads <= 0) return YOHO_OK;
+  {
+    // four-tile kernel (attention4_sm100.cu) when 512-row work items pad the sequence no further than 256-row ones
+    static const int forced = [] { const char* e = getenv("YOHO_ATT_TILES"); return e ? atoi(e) : 0; }();
+    const bool same_pad = ceil_div(t, 512) * 512 == ceil_div(t, kItemQ) * kItemQ;
+    if (forced == 4 || (forced != 2 && same_pad)) return launch_attention4_bf16(ctx, qkv, out, batch, t, heads, s);
+  }
   const int dims = heads * kHeadDim;
   AttParams p{};
   p.t_len = t; p.dims = dims; p.heads = heads;

@@ -53,8 +53,15 @@ template <int BN> struct GemmCfg {
   static constexpr int kABytes = kBlockM * kBlockK * 2;          // 16 KB
   static constexpr int kBBytes = (BN / 2) * kBlockK * 2;         // this CTA's half of the B tile
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = BN == 256 ? 5 : 6;
-  static constexpr int kStagingBytes = kEpiWarps * 2 * kStageBufBytes;   // 64 KB
+  // Operand ring depth decides how much TMA latency the MMA stream tolerates: with 5 stages of 32 KB the issuer waited on
+  // full_bar for ~2/3 of its time (ncu, tensor pipe 75 % active).  BN = 256 therefore gives the epilogue warps one
+  // staging buffer each (they are far off the critical path) and spends the 32 KB on a sixth operand stage.
+#ifndef YOHO_GEMM_STAGES_256
+#define YOHO_GEMM_STAGES_256 6
+#endif
+  static constexpr int kStages = BN == 256 ? YOHO_GEMM_STAGES_256 : 6;
+  static constexpr int kEpiBufs = (BN == 256 && kStages > 5) ? 1 : 2;     // staging buffers per epilogue warp
+  static constexpr int kStagingBytes = kEpiWarps * kEpiBufs * kStageBufBytes;   // 32 or 64 KB
   static constexpr int kTmemCols = 2 * BN;
   static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
   static_assert(kSmemBytes <= 232448, "exceeds the 227 KB dynamic shared memory limit");
@@ -202,7 +209,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // ===================== epilogue: TMEM -> registers -> swizzled smem -> TMA store / reduce-add =====================
     const int q = warp & 3;          // the TMEM lane quadrant this warp may read
     const int half = (warp - 4) >> 2;  // which of the two warps of the quadrant: takes column chunks half, half + 2, ...
-    unsigned char* my_stage = staging + (warp - 4) * 2 * kStageBufBytes;
+    unsigned char* my_stage = staging + (warp - 4) * Cfg::kEpiBufs * kStageBufBytes;
     const int sw = lane & 7;
     int buf = 0;
     int it = 0;
@@ -233,7 +240,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
             epilogue_math(v, p, col0, pos_row, masked);
             unsigned char* sbuf = my_stage + buf * kStageBufBytes;
-            if (lane == 0) tma_store_wait_read<1>();     // the buffer written two chunks ago has been read out
+            if (lane == 0) tma_store_wait_read<Cfg::kEpiBufs - 1>();     // the previous user of this buffer has been read out
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < 8; ++j)
@@ -245,7 +252,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
               else tma_store_3d(&map_c, sbuf, col0, warp_row0, b);
               tma_store_commit();
             }
-            buf ^= 1;
+            buf = (buf + 1) % Cfg::kEpiBufs;
           }
         } else {
           // 64 bf16 columns (= 128 B rows) per staging buffer
@@ -258,7 +265,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             tmem_ld_32x32b_x32(t_addr + uint32_t(c * 64 + 32), acc1);
             tmem_ld_wait();
             unsigned char* sbuf = my_stage + buf * kStageBufBytes;
-            if (lane == 0) tma_store_wait_read<1>();
+            if (lane == 0) tma_store_wait_read<Cfg::kEpiBufs - 1>();
             __syncwarp();
             {
               float v[32];
@@ -288,7 +295,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
               tma_store_3d(&map_c, sbuf, col0, warp_row0, b);   // columns >= n and rows >= rows_per_batch are clipped
               tma_store_commit();
             }
-            buf ^= 1;
+            buf = (buf + 1) % Cfg::kEpiBufs;
           }
         }
       }
