@@ -1,27 +1,25 @@
-// Fused self-attention forward, four query tiles per CTA (sm_100a).  Same contract as attention_sm100.cu:
+// Fused self-attention forward, three query tiles per CTA (sm_100a).  Same contract as attention_sm100.cu:
 //   out = softmax(q k^T / sqrt(64)) v   per (clip, head), no mask      (reference whisper.py:52-67)
 //
 // Why a second kernel: at d_head = 64 the bound is the SFU (16 ex2/clk/SM = 1024 clk per 128 x 128 score tile
 // against 512 clk of MMA).  The two-tile kernel keeps two softmax warps per sub-partition; they run in phase
 // (both wait for the same K/V tile), so a step pair costs 2 E + N clocks (E = 512 clk of exp2, N = ~450 clk of
 // mbarrier wait -> tcgen05.ld -> row max -> vote -> ... -> tcgen05.st -> arrive latency during which the SFU idles).
-// Here a work item is (clip, head, 512 query rows) = FOUR 128-row query tiles sharing every K/V tile, i.e. four
-// softmax warps per sub-partition whose N phases hide behind the other three warps' exp2 blocks.
+// Here a work item is (clip, head, 384 query rows) = THREE 128-row query tiles sharing every K/V tile, i.e. three
+// softmax warps per sub-partition whose N phases hide behind the other warps' exp2 blocks, and the tensor-core
+// round trip is taken off the softmax warps' path altogether (below).
 //
-// CTA = 21 warps (672 threads, 96 registers each):
-//   warps 0-15   softmax of tile t = warp / 4, TMEM lanes 32 (warp % 4) .. +31  (thread = one query row)
-//   warp 16      TMA producer: Q tiles (double buffered across items), K_j / V_j rings of 64 keys (= 1 step)
-//   warps 17-20  MMA issuer of tile t = warp - 17 (warp 17 also allocates TMEM)
+// CTA = 16 warps (512 threads, up to 128 registers each):
+//   warps 0-11   softmax of tile t = warp / 4, TMEM lanes 32 (warp % 4) .. +31  (thread = one query row)
+//   warp 12      TMA producer: Q tiles (double buffered across items), K_j / V_j rings of 64 keys (= 1 step)
+//   warps 13-15  MMA issuer of tile t = warp - 13 (warp 13 also allocates TMEM)
 // Per step g (64 keys) and tile t:   S_t = Q_t K_g^T   (M128 N64 K64, operands in shared memory)
 //                                    O_t += P_t V_g    (M128 N64 K64, P read from TMEM, V MN-major)
-// TMEM (all 512 columns): S_t = 64 fp32 columns at 64 t, O_t = 64 columns at 256 + 64 t; P_t (packed bf16) is
-// written over the first 32 columns of S_t.  S is single buffered per tile: the chain softmax(g) -> P V(g) ->
-// Q K^T(g+1) -> softmax(g+1) of one tile is serial, and the other three tiles of the sub-partition fill the gap.
-// With 96 registers a softmax thread cannot hold its 64 scores and the 32 packed P words at once, so the scores are
-// read in two 32-column halves: maxima of both halves first (the second half stays in registers), then exp2 of the
-// second half, then the first half is read again.  O stays in TMEM and is rescaled only when the running maximum
-// grows by more than 2^8 (lazy rescaling); s_full(g) implies P V(g-1) has retired (same issuing thread, in-order
-// commit), so the rescale needs no barrier of its own.
+// TMEM: S_t = 64 fp32 columns at 64 t, O_t = 64 columns at 192 + 64 t, P_t = 32 columns of packed bf16 at
+// 384 + 32 t.  P has columns of its own, so S_t is handed back (s_free) as soon as the softmax warps hold the 64
+// scores of step g in registers: Q K^T of step g+1 runs while they exponentiate step g and is finished when they
+// get there -- one S buffer per tile is enough and the MMA issue / pipe latency never shows.  O stays in TMEM and
+// is rescaled only when the running maximum grows by more than 2^8 (lazy rescaling).
 #include "kernels.cuh"
 #include "ptx_sm100.cuh"
 
@@ -31,16 +29,16 @@ using namespace ptx;
 
 namespace att4 {
 
-constexpr int kTiles = 4;
+constexpr int kTiles = 3;
 constexpr int kSoftmaxWarps = 4 * kTiles;
-constexpr int kThreads = (kSoftmaxWarps + 1 + kTiles) * 32;   // 672
+constexpr int kThreads = (kSoftmaxWarps + 1 + kTiles) * 32;   // 512
 constexpr int kTileQ = 128, kStepKV = 64, kHeadDim = 64;
-constexpr int kItemQ = kTiles * kTileQ;          // 512 query rows per work item
+constexpr int kItemQ = kTiles * kTileQ;          // 384 query rows per work item
 constexpr int kQBytes = kTileQ * kHeadDim * 2;   // 16 KB
 constexpr int kKvBytes = kStepKV * kHeadDim * 2; // 8 KB
 constexpr int kKvStages = 6;
 constexpr uint32_t kTmemCols = 512;
-constexpr uint32_t kTmemS = 0, kTmemO = 256;     // S_t at 64 t, O_t at 256 + 64 t
+constexpr uint32_t kTmemS = 0, kTmemO = 64 * kTiles, kTmemP = 128 * kTiles;   // S_t at 64 t, O_t at 192 + 64 t, P_t at 384 + 32 t
 constexpr float kRescaleLog2 = 8.0f;
 #ifndef YOHO_ATT4_WAIT_NS
 #define YOHO_ATT4_WAIT_NS 2000
@@ -48,12 +46,13 @@ constexpr float kRescaleLog2 = 8.0f;
 constexpr uint32_t kWaitHintNs = YOHO_ATT4_WAIT_NS;   // suspend hint of the softmax warps' waits (see mbar_wait_hint)
 
 struct Smem {
-  unsigned char q[2][kTiles][kQBytes];   // [item slot][query tile]      128 KB
+  unsigned char q[2][kTiles][kQBytes];   // [item slot][query tile]       96 KB
   unsigned char k[kKvStages][kKvBytes];  //                               48 KB
   unsigned char v[kKvStages][kKvBytes];  //                               48 KB
   uint64_t q_full[2][kTiles], q_empty[2][kTiles];
   uint64_t k_full[kKvStages], k_empty[kKvStages], v_full[kKvStages], v_empty[kKvStages];
   uint64_t s_full[kTiles], p_full[kTiles];
+  uint64_t s_free[kTiles], p_free[kTiles];   // S_t is in the softmax warps' registers / P_t has been consumed by its P V
   uint64_t o_last[kTiles], o_free[kTiles];   // last P V of an item has retired / O has been read out
   uint32_t tmem_slot;
 };
@@ -61,7 +60,7 @@ static_assert(sizeof(Smem) + 1024 <= 232448, "attention x4: shared memory");
 
 struct Params {
   int t_len, dims, heads;
-  int q_blocks;      // ceil(t_len / 512)
+  int q_blocks;      // ceil(t_len / 384)
   int n_items;       // batch * heads * q_blocks
   int n_steps;       // ceil(t_len / 64)
 };
@@ -77,6 +76,33 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
   return y;
 }
 
+// exp2 of a pair on the FMA pipe (no MUFU): x = n + f with n = round(x), f in [-0.5, 0.5]; 2^f by a degree-3
+// minimax polynomial (7.5e-5 relative, well under the bf16 rounding of P), 2^n by adding n to the exponent field.
+// t = x + 1.5 * 2^23 holds n in its low mantissa bits; x is clamped to -126 first (masked keys are -inf).
+__device__ __forceinline__ void exp2_poly_pair(float& lo, float& hi) {
+  const uint64_t magic = pack_f32x2(12582912.0f, 12582912.0f), neg_magic = pack_f32x2(-12582912.0f, -12582912.0f);
+  const uint64_t neg_one = pack_f32x2(-1.0f, -1.0f);
+  const uint64_t k0 = pack_f32x2(0.9999280571937561f, 0.9999280571937561f), k1 = pack_f32x2(0.6932609677314758f, 0.6932609677314758f);
+  const uint64_t k2 = pack_f32x2(0.2426111251115799f, 0.2426111251115799f), k3 = pack_f32x2(0.05517164617776871f, 0.05517164617776871f);
+  const uint64_t x = pack_f32x2(fmaxf(lo, -126.0f), fmaxf(hi, -126.0f));
+  const uint64_t t = add_f32x2(x, magic);
+  const uint64_t f = fma_f32x2(add_f32x2(t, neg_magic), neg_one, x);
+  const uint64_t q = fma_f32x2(fma_f32x2(fma_f32x2(k3, f, k2), f, k1), f, k0);
+  float t_lo, t_hi, q_lo, q_hi;
+  unpack_f32x2(t, t_lo, t_hi);
+  unpack_f32x2(q, q_lo, q_hi);
+  lo = __int_as_float(__float_as_int(q_lo) + (__float_as_int(t_lo) << 23));
+  hi = __int_as_float(__float_as_int(q_hi) + (__float_as_int(t_hi) << 23));
+}
+
+#ifndef YOHO_ATT_POLY_EVERY
+#define YOHO_ATT_POLY_EVERY 4
+#endif
+// every kPolyEvery-th pair of a row takes the polynomial instead of the SFU (0 = none): the SFU is the bound of this
+// kernel (ncu: MUFU queue full for most of the softmax warps' stall samples) while the FMA pipe is ~13 % busy
+constexpr int kPolyEvery = YOHO_ATT_POLY_EVERY;
+__device__ __forceinline__ constexpr bool poly_pair(int i) { return kPolyEvery > 0 && ((i >> 1) % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyEvery - 1; }
+
 // exp2(s c - mc) of 32 scores -> 16 packed bf16x2 words; returns the sum of the 32 (unrounded) exponentials.
 // Scale / shift and the sum run on packed fp32 pairs (FFMA2 / FADD2); the exponentials are issued one block of 8
 // ahead of their consumers so that the in-order warp does not wait on a MUFU result with the SFU idle.
@@ -87,16 +113,17 @@ __device__ __forceinline__ float exp_pack32(const uint32_t (&s)[32], uint64_t c2
     unpack_f32x2(fma_f32x2(pack_f32x2(__uint_as_float(s[i]), __uint_as_float(s[i + 1])), c2, nmc2), x[i], x[i + 1]);
   constexpr int kBlk = 8;
 #pragma unroll
-  for (int i = 0; i < kBlk; ++i) x[i] = ex2_approx(x[i]);
+  for (int i = 0; i < kBlk; ++i) if (!poly_pair(i)) x[i] = ex2_approx(x[i]);
   uint64_t l01 = 0, l23 = 0;
 #pragma unroll
   for (int blk = 0; blk < 32 / kBlk; ++blk) {
     if (blk + 1 < 32 / kBlk) {
 #pragma unroll
-      for (int i = 0; i < kBlk; ++i) x[(blk + 1) * kBlk + i] = ex2_approx(x[(blk + 1) * kBlk + i]);
+      for (int i = 0; i < kBlk; ++i) if (!poly_pair((blk + 1) * kBlk + i)) x[(blk + 1) * kBlk + i] = ex2_approx(x[(blk + 1) * kBlk + i]);
     }
 #pragma unroll
     for (int i = blk * kBlk; i < (blk + 1) * kBlk; i += 2) {
+      if (poly_pair(i)) exp2_poly_pair(x[i], x[i + 1]);
       if (blk & 1) l23 = add_f32x2(l23, pack_f32x2(x[i], x[i + 1]));
       else l01 = add_f32x2(l01, pack_f32x2(x[i], x[i + 1]));
       __nv_bfloat162 u = __floats2bfloat162_rn(x[i], x[i + 1]);
@@ -137,6 +164,7 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
     }
     for (int t = 0; t < kTiles; ++t) {
       mbar_init(&sm.s_full[t], 1); mbar_init(&sm.p_full[t], 4);
+      mbar_init(&sm.s_free[t], 4); mbar_init(&sm.p_free[t], 1);
       mbar_init(&sm.o_last[t], 1); mbar_init(&sm.o_free[t], 4);
     }
     fence_mbar_init();
@@ -183,7 +211,7 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
     }
     __syncwarp();
   } else if (warp > kSoftmaxWarps) {
-    // ===================== MMA issuers: warp 17 + t drives query tile t =====================
+    // ===================== MMA issuers: warp 13 + t drives query tile t =====================
     // The warp stays converged and one elected lane issues (umma_*_w); descriptors are linear in (slot, stage, k step).
     const int t = warp - (kSoftmaxWarps + 1);
     constexpr uint32_t idesc_qk = make_idesc_bf16(kTileQ, kStepKV, 0, 0);   // A = Q (K-major), B = K (K-major)
@@ -193,6 +221,7 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
     const uint64_t kdesc0 = make_desc_sw128(smem_u32(sm.k[0]), 16, 1024);          // stage st: + st kKvStageDesc
     const uint64_t vdesc0 = make_desc_sw128(smem_u32(sm.v[0]), 1024, 1024);
     const uint32_t s_tmem = tmem_base + kTmemS + uint32_t(t * 64), o_tmem = tmem_base + kTmemO + uint32_t(t * 64);
+    const uint32_t p_tmem = tmem_base + kTmemP + uint32_t(t * 32);
     const int g_total = n_my * n_steps;
     // Q K^T cursor (one step ahead of P V)
     int q_it = 0, q_j = 0, q_st = 0; uint32_t q_ph = 0;
@@ -218,11 +247,15 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
     int p_it = 0, p_j = 0, p_st = 0; uint32_t p_ph = 0;
     for (int g = 0; g < g_total; ++g) {
       const bool last = p_j == n_steps - 1;
-      const bool more = g + 1 < g_total;
-      // everything that does not depend on the softmax of this step first: between p_full and the commit of
-      // s_full(g+1) -- the round trip the softmax warps of this tile sit out -- only the eight MMAs are issued
+      // Q K^T one step ahead: S_t is free as soon as the softmax warps have read the scores of step g
+      if (g + 1 < g_total) {
+        qk_operands();
+        mbar_wait(&sm.s_free[t], g & 1);
+        tc_fence_after();
+        qk_mma();
+        qk_release();
+      }
       mbar_wait(&sm.v_full[p_st], p_ph);
-      if (more) qk_operands();
       if (p_j == 0 && p_it > 0) mbar_wait(&sm.o_free[t], (p_it - 1) & 1);    // previous item's O has been read out
       const uint64_t bdesc = vdesc0 + uint64_t(p_st) * kKvStageDesc;
       mbar_wait(&sm.p_full[t], g & 1);                                       // P in TMEM, O rescaled if needed
@@ -230,13 +263,12 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
       // A: 16 keys = 8 packed columns.  B: V rows are keys (128 B each): 16 keys = 2 groups of 8 rows, 1024 B apart
 #pragma unroll
       for (int ks = 0; ks < kStepKV / 16; ++ks)
-        umma_bf16_ts_w(o_tmem, s_tmem + uint32_t(ks * 8), bdesc + uint64_t(ks * (2048 >> 4)), idesc_pv, (p_j | ks) != 0);
-      if (more) qk_mma();                     // in pipe order after P V(g): S_t / P_t may be overwritten
+        umma_bf16_ts_w(o_tmem, p_tmem + uint32_t(ks * 8), bdesc + uint64_t(ks * (2048 >> 4)), idesc_pv, (p_j | ks) != 0);
+      umma_commit_w(&sm.p_free[t]);
       if (last) umma_commit_w(&sm.o_last[t]);
       umma_commit_w(&sm.v_empty[p_st]);
       if (++p_st == kKvStages) { p_st = 0; p_ph ^= 1; }
       if (last) { p_j = 0; ++p_it; } else { ++p_j; }
-      if (more) qk_release();
     }
     __syncwarp();
   } else {
@@ -246,6 +278,7 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
     const uint32_t lane_base = tmem_base + (uint32_t((warp & 3) * 32) << 16);
     const uint32_t s_addr = lane_base + kTmemS + uint32_t(t * 64);
     const uint32_t o_addr = lane_base + kTmemO + uint32_t(t * 64);
+    const uint32_t p_addr = lane_base + kTmemP + uint32_t(t * 32);
     const float c = 0.125f * 1.4426950408889634f;            // d_head^-0.5 * log2(e)   (whisper.py:54-57)
     const uint64_t c2 = pack_f32x2(c, c);
     const int kv_tail = p.t_len - (n_steps - 1) * kStepKV;    // valid keys of the last step
@@ -258,32 +291,31 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
       for (int j = 0; j < n_steps; ++j, ++g) {
         mbar_wait_hint(&sm.s_full[t], g & 1, kWaitHintNs);
         tc_fence_after();
-        const bool tail = j == n_steps - 1 && kv_tail < kStepKV;      // CTA-uniform
-        uint32_t sv[32];
-        // ---- pass 1: row maximum over both halves (the second half stays in registers)
-        tmem_ld_32x32b_x32(s_addr, sv);
+        uint32_t a[32], b[32];
+        tmem_ld_32x32b_x32(s_addr, a);
+        tmem_ld_32x32b_x32(s_addr + 32, b);
         tmem_ld_wait();
-        if (tail) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.s_free[t]);            // the scores are in registers: S_t may take Q K^T of step g + 1
+        if (j == n_steps - 1 && kv_tail < kStepKV) {          // CTA-uniform
 #pragma unroll
-          for (int i = 0; i < 32; ++i) if (i >= kv_tail) sv[i] = 0xff800000u;       // -inf: exp2 gives exactly 0
+          for (int i = 0; i < 32; ++i) {
+            if (i >= kv_tail) a[i] = 0xff800000u;               // -inf: exp2 gives exactly 0
+            if (32 + i >= kv_tail) b[i] = 0xff800000u;
+          }
         }
-        const float m_a = max32(sv);
-        tmem_ld_32x32b_x32(s_addr + 32, sv);
-        tmem_ld_wait();
-        if (tail) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) if (32 + i >= kv_tail) sv[i] = 0xff800000u;
-        }
-        const float m_tile = fmaxf(m_a, max32(sv));
+        const float m_tile = fmaxf(max32(a), max32(b));
         if (j == 0) {
           m_ref = m_tile;
         } else if (__any_sync(0xffffffffu, (m_tile - m_ref) * c > kRescaleLog2)) {
-          // rare: the running maximum grew by more than 2^8 somewhere in this warp -> rescale O and l.
-          // s_full(g) was committed after P V(g-1) by the same thread, so O is quiescent here.
+          // rare: the running maximum grew by more than 2^8 somewhere in this warp -> rescale O and l
           const float m_new = fmaxf(m_ref, m_tile);
           const float alpha = ex2_approx((m_ref - m_new) * c);
           m_ref = m_new;
           l_run *= alpha;
+          mbar_wait(&sm.p_free[t], (g - 1) & 1);              // P V of the previous step has retired: O is quiescent
+          tc_fence_after();
 #pragma unroll
           for (int h = 0; h < 4; ++h) {
             uint32_t o[16];
@@ -295,18 +327,15 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
           }
           tmem_st_wait();
         }
-        // ---- pass 2: exponentials, second half first (already in registers), then the first half again
         const uint64_t nmc2 = pack_f32x2(-m_ref * c, -m_ref * c);
         uint32_t packed[32];
-        l_run += exp_pack32(sv, c2, nmc2, packed + 16);
-        tmem_ld_32x32b_x32(s_addr, sv);
-        tmem_ld_wait();
-        if (tail) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) if (i >= kv_tail) sv[i] = 0xff800000u;
+        l_run += exp_pack32(a, c2, nmc2, packed);
+        l_run += exp_pack32(b, c2, nmc2, packed + 16);
+        if (g > 0) {                                          // P_t feeds P V of step g - 1 until that MMA retires (long done)
+          mbar_wait(&sm.p_free[t], (g - 1) & 1);
+          tc_fence_after();
         }
-        l_run += exp_pack32(sv, c2, nmc2, packed);
-        tmem_st_32x32b_x32(s_addr, packed);      // P over the first 32 (now consumed) columns of S_t
+        tmem_st_32x32b_x32(p_addr, packed);
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
