@@ -40,10 +40,6 @@ constexpr int kKvStages = 6;
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kTmemS = 0, kTmemO = 64 * kTiles, kTmemP = 128 * kTiles;   // S_t at 64 t, O_t at 192 + 64 t, P_t at 384 + 32 t
 constexpr float kRescaleLog2 = 8.0f;
-#ifndef YOHO_ATT4_WAIT_NS
-#define YOHO_ATT4_WAIT_NS 2000
-#endif
-constexpr uint32_t kWaitHintNs = YOHO_ATT4_WAIT_NS;   // suspend hint of the softmax warps' waits (see mbar_wait_hint)
 
 struct Smem {
   unsigned char q[2][kTiles][kQBytes];   // [item slot][query tile]       96 KB
@@ -192,17 +188,17 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
         const int head = ch % p.heads, clip = ch / p.heads;
         const int slot = it & 1; const uint32_t qph = (it >> 1) & 1;
         for (int t = 0; t < kTiles; ++t) {
-          mbar_wait(&sm.q_empty[slot][t], qph ^ 1);
+          mbar_wait_idle(&sm.q_empty[slot][t], qph ^ 1);
           mbar_arrive_expect_tx(&sm.q_full[slot][t], kQBytes);
           // the tensor map's box is 64 rows (one K/V step): a query tile is two boxes
           tma_load_3d(sm.q[slot][t], &map_qkv, &sm.q_full[slot][t], head * kHeadDim, qb * kItemQ + t * kTileQ, clip);
           tma_load_3d(sm.q[slot][t] + kKvBytes, &map_qkv, &sm.q_full[slot][t], head * kHeadDim, qb * kItemQ + t * kTileQ + 64, clip);
         }
         for (int j = 0; j < n_steps; ++j) {
-          mbar_wait(&sm.k_empty[st], ph ^ 1);
+          mbar_wait_idle(&sm.k_empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&sm.k_full[st], kKvBytes);
           tma_load_3d(sm.k[st], &map_qkv, &sm.k_full[st], p.dims + head * kHeadDim, j * kStepKV, clip);
-          mbar_wait(&sm.v_empty[st], ph ^ 1);
+          mbar_wait_idle(&sm.v_empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&sm.v_full[st], kKvBytes);
           tma_load_3d(sm.v[st], &map_qkv, &sm.v_full[st], 2 * p.dims + head * kHeadDim, j * kStepKV, clip);
           if (++st == kKvStages) { st = 0; ph ^= 1; }
@@ -258,7 +254,7 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
       mbar_wait(&sm.v_full[p_st], p_ph);
       if (p_j == 0 && p_it > 0) mbar_wait(&sm.o_free[t], (p_it - 1) & 1);    // previous item's O has been read out
       const uint64_t bdesc = vdesc0 + uint64_t(p_st) * kKvStageDesc;
-      mbar_wait(&sm.p_full[t], g & 1);                                       // P in TMEM, O rescaled if needed
+      mbar_wait_idle(&sm.p_full[t], g & 1);                                       // P in TMEM, O rescaled if needed
       tc_fence_after();
       // A: 16 keys = 8 packed columns.  B: V rows are keys (128 B each): 16 keys = 2 groups of 8 rows, 1024 B apart
 #pragma unroll
@@ -289,7 +285,7 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
       const int head = ch % p.heads, clip = ch / p.heads;
       float m_ref = -INFINITY, l_run = 0.0f;
       for (int j = 0; j < n_steps; ++j, ++g) {
-        mbar_wait_hint(&sm.s_full[t], g & 1, kWaitHintNs);
+        mbar_wait_idle(&sm.s_full[t], g & 1);
         tc_fence_after();
         uint32_t a[32], b[32];
         tmem_ld_32x32b_x32(s_addr, a);
@@ -342,7 +338,7 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
         if (lane == 0) mbar_arrive(&sm.p_full[t]);
       }
       // last P V of the item: pull O into registers (two halves), hand O_t back to the MMA warp, normalise and store
-      mbar_wait_hint(&sm.o_last[t], it & 1, kWaitHintNs);
+      mbar_wait_idle(&sm.o_last[t], it & 1);
       tc_fence_after();
       const float inv_l = 1.0f / l_run;
       const int t_row = qb * kItemQ + t * kTileQ + row;

@@ -59,6 +59,16 @@ __device__ __forceinline__ void mbar_wait_hint(uint64_t* bar, uint32_t parity, u
       ::"r"(smem_u32(bar)), "r"(parity), "r"(ns) : "memory");
 }
 
+// Waits of warps that are off the critical path (epilogue warps waiting for an accumulator, producers waiting for a
+// free slot, MMA warps waiting for the softmax): suspend in hardware instead of polling (power, issue slots).
+#ifndef YOHO_IDLE_WAIT_NS
+#define YOHO_IDLE_WAIT_NS 1000
+#endif
+__device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity) {
+  if (YOHO_IDLE_WAIT_NS > 0) mbar_wait_hint(bar, parity, YOHO_IDLE_WAIT_NS);
+  else mbar_wait(bar, parity);
+}
+
 // ---------------------------------------------------------------- named barriers (ids 1-15; 0 is __syncthreads)
 __device__ __forceinline__ void named_bar_sync(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
