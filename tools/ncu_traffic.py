@@ -6,7 +6,7 @@ Writes {class: {"bytes_per_launch_per_clip": ..., "launches": n, "clips": c, "so
 by the clips of its own launches to fill roofline.traffic (dram__bytes_read.sum + dram__bytes_write.sum)."""
 import csv, io, json, subprocess, sys
 
-CLASS = {"gemm_bf16_kernel": "gemm_tcgen05", "attention_bf16_kernel": "attention_tcgen05", "logmel_kernel": "logmel",
+CLASS = {"gemm_bf16_kernel": "gemm_tcgen05", "attention_bf16_kernel": "attention_tcgen05", "attention3_bf16_kernel": "attention_tcgen05", "logmel_kernel": "logmel",
          "layernorm_kernel": "layernorm", "normalize_apply_kernel": "normalize"}
 # the log-mel kernel is persistent (1-D grid), so the clips of the captured launch are given: prof_case.py runs it
 # over max(clips, 128) clips in launches of <= 52 (one L2-resident chunk), and the capture takes a full one

@@ -19,7 +19,7 @@ LIB_DIR = ROOT / "yoho_b200" / "lib"
 LIB = LIB_DIR / "libyoho_b200.so"
 OBJ_DIR = ROOT / "build" / "obj"
 
-SOURCES = ["api.cu", "frontend.cu", "elementwise.cu", "encoder_fp32.cu", "gemm_sm100.cu", "attention_sm100.cu", "attention4_sm100.cu", "encoder.cu", "yoho_ops.cu", "yoho_model.cu", "crosskv.cu", "decoder_ops.cu", "decoder.cu", "xla_ffi.cc"]
+SOURCES = ["api.cu", "frontend.cu", "elementwise.cu", "encoder_fp32.cu", "gemm_sm100.cu", "attention_sm100.cu", "attention3_sm100.cu", "encoder.cu", "yoho_ops.cu", "yoho_model.cu", "crosskv.cu", "decoder_ops.cu", "decoder.cu", "xla_ffi.cc"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",

@@ -27,7 +27,7 @@ namespace yoho {
 
 using namespace ptx;
 
-namespace att4 {
+namespace att3 {
 
 constexpr int kTiles = 3;
 constexpr int kSoftmaxWarps = 4 * kTiles;
@@ -52,7 +52,7 @@ struct Smem {
   uint64_t o_last[kTiles], o_free[kTiles];   // last P V of an item has retired / O has been read out
   uint32_t tmem_slot;
 };
-static_assert(sizeof(Smem) + 1024 <= 232448, "attention x4: shared memory");
+static_assert(sizeof(Smem) + 1024 <= 232448, "attention x3: shared memory");
 
 struct Params {
   int t_len, dims, heads;
@@ -144,14 +144,14 @@ __device__ __forceinline__ float max32(const uint32_t (&s)[32]) {
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, const Params p) {
-  extern __shared__ __align__(1024) unsigned char att4_smem_raw[];
-  Smem& sm = *reinterpret_cast<Smem*>(att4_smem_raw);
+attention3_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16* __restrict__ out, const Params p) {
+  extern __shared__ __align__(1024) unsigned char att3_smem_raw[];
+  Smem& sm = *reinterpret_cast<Smem*>(att3_smem_raw);
   // warp index through a shuffle: warp-uniform for ptxas (role branches and the MMA warps' loops stay on the uniform datapath)
   const int warp = __shfl_sync(0xffffffffu, int(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
-    if (smem_u32(att4_smem_raw) & 1023u) __trap();  // operand tiles need 1024-byte alignment (128B swizzle)
+    if (smem_u32(att3_smem_raw) & 1023u) __trap();  // operand tiles need 1024-byte alignment (128B swizzle)
     for (int s = 0; s < 2; ++s)
       for (int t = 0; t < kTiles; ++t) { mbar_init(&sm.q_full[s][t], 1); mbar_init(&sm.q_empty[s][t], 1); }
     for (int i = 0; i < kKvStages; ++i) {
@@ -371,10 +371,10 @@ attention4_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
   if (warp == kSoftmaxWarps + 1) tmem_dealloc<kTmemCols>(tmem_base);
 }
 
-}  // namespace att4
+}  // namespace att3
 
-int launch_attention4_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16* out, int batch, int t, int heads, cudaStream_t s) {
-  using namespace att4;
+int launch_attention3_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16* out, int batch, int t, int heads, cudaStream_t s) {
+  using namespace att3;
   if (!qkv || !out) return fail(YOHO_ERR_INVALID, "attention: null operand");
   if (batch <= 0 || t <= 0 || heads <= 0) return YOHO_OK;
   const int dims = heads * kHeadDim;
@@ -389,11 +389,11 @@ int launch_attention4_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat1
   int r = make_tmap_bf16_3d(ctx->encode_tiled, &map, qkv, uint64_t(3 * dims), uint64_t(t), uint64_t(batch), uint64_t(3 * dims),
                             uint64_t(3 * dims) * uint64_t(t), kHeadDim, kStepKV, 1);
   if (r) return fail(YOHO_ERR_CUDA, "attention: cuTensorMapEncodeTiled failed with CUresult %d", r);
-  YOHO_CUDA_CHECK(cudaFuncSetAttribute(attention4_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(Smem))));
+  YOHO_CUDA_CHECK(cudaFuncSetAttribute(attention3_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(Smem))));
   const int grid = p.n_items < ctx->num_sms ? p.n_items : ctx->num_sms;
   ProfScope prof(s, kProfAttention, 4.0 * double(batch) * double(t) * double(t) * double(dims));
-  attention4_bf16_kernel<<<grid, kThreads, sizeof(Smem), s>>>(map, out, p);
-  YOHO_LAUNCH_CHECK("attention4_bf16_kernel");
+  attention3_bf16_kernel<<<grid, kThreads, sizeof(Smem), s>>>(map, out, p);
+  YOHO_LAUNCH_CHECK("attention3_bf16_kernel");
   return YOHO_OK;
 }
 

@@ -369,10 +369,10 @@ int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16
   if (!qkv || !out) return fail(YOHO_ERR_INVALID, "attention: null operand");
   if (batch <= 0 || t <= 0 || heads <= 0) return YOHO_OK;
   {
-    // three-tile kernel (attention4_sm100.cu) when 384-row work items pad the sequence no further than 256-row ones
+    // three-tile kernel (attention3_sm100.cu) when 384-row work items pad the sequence no further than 256-row ones
     static const int forced = [] { const char* e = getenv("YOHO_ATT_TILES"); return e ? atoi(e) : 0; }();
     const bool pad_ok = ceil_div(t, 384) * 384 <= ceil_div(t, kItemQ) * kItemQ;
-    if (forced == 3 || (forced != 2 && pad_ok)) return launch_attention4_bf16(ctx, qkv, out, batch, t, heads, s);
+    if (forced == 3 || (forced != 2 && pad_ok)) return launch_attention3_bf16(ctx, qkv, out, batch, t, heads, s);
   }
   const int dims = heads * kHeadDim;
   AttParams p{};

@@ -106,8 +106,8 @@ int launch_gemm_bf16(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s);
 // ---------------------------------------------------------------- attention_sm100.cu (tcgen05)
 // qkv (batch, t, 3*dims) bf16 with q | k | v column blocks, heads of 64; out (batch, t, dims) bf16.
 int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16* out, int batch, int t, int heads, cudaStream_t s);
-// attention4_sm100.cu: three query tiles (384 rows) per work item; launch_attention_bf16 dispatches to it when that
+// attention3_sm100.cu: three query tiles (384 rows) per work item; launch_attention_bf16 dispatches to it when that
 // pads the sequence no further than 256-row items do (YOHO_ATT_TILES=2|3 forces one of them)
-int launch_attention4_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16* out, int batch, int t, int heads, cudaStream_t s);
+int launch_attention3_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16* out, int batch, int t, int heads, cudaStream_t s);
 
 }  // namespace yoho
