@@ -325,6 +325,9 @@ int yoho_test_gemm_bf16(yoho_ctx* ctx, const float* a, const float* w, const flo
 size_t yoho_test_attention_workspace_bytes(int batch, int t, int heads);
 int yoho_test_attention_bf16(yoho_ctx* ctx, const float* qkv, float* out, int batch, int t, int heads,
                              void* ws, size_t ws_bytes, yoho_stream_t stream);
+/* which attention kernel serves the calls that follow: 0 = chosen by padding (default), 2 = two query tiles per work
+ * item, 3 = three; returns the previous setting.  Process-wide, for tests and A/B timing only. */
+int yoho_test_attention_tiles(int tiles);
 /* out (b, n) (+)= act(x (b, k) @ w (k, n) + bias): the decoder's weight-streaming GEMM in isolation */
 int yoho_test_skinny_gemm(yoho_ctx* ctx, const float* x, const float* w, const float* bias, float* out, int b,
                           int k, int n, int gelu, int accumulate, yoho_stream_t stream);

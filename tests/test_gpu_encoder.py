@@ -57,12 +57,11 @@ def test_tcgen05_gemm(rt, m, n, k, epi):
 
 
 # ------------------------------------------------------------------ tcgen05 attention in isolation
-@pytest.mark.parametrize("batch,t,heads", [(1, 128, 1), (2, 100, 2), (1, 1500, 2), (3, 300, 6), (2, 257, 1)])
-def test_tcgen05_attention(rt, batch, t, heads):
+def _attention_case(rt, qkv, tiles):
+    """softmax(q k^T / 8) v through the C ABI with the chosen kernel (0 = automatic dispatch) vs float64 numpy."""
     import torch
-    rng = np.random.default_rng(batch * 1000 + t + heads)
-    qkv = rng.standard_normal((batch, t, 3, heads, 64)).astype(np.float32)
-    qkv[:, :, 0] *= 2.0                                                  # sharper softmax
+    from yoho_b200._lib import check
+    batch, t, _, heads, _ = qkv.shape
     r = _bf16(qkv).astype(np.float64)
     q, k, v = (r[:, :, i].transpose(0, 2, 1, 3) for i in range(3))       # (B, H, T, 64)
     s = q @ k.transpose(0, 1, 3, 2) / 8.0
@@ -73,13 +72,53 @@ def test_tcgen05_attention(rt, batch, t, heads):
     out = torch.full((batch, t, heads * 64), float("nan"), device="cuda")
     nbytes = rt.lib.yoho_test_attention_workspace_bytes(batch, t, heads)
     ws = rt.workspace("test", nbytes)
-    from yoho_b200._lib import check
-    check(rt.lib.yoho_test_attention_bf16(rt.ctx, C.c_void_p(qd.data_ptr()), C.c_void_p(out.data_ptr()), batch, t, heads,
-                                          C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
-    torch.cuda.synchronize()
-    got = out.cpu().numpy()
+    prev = rt.lib.yoho_test_attention_tiles(tiles)
+    try:
+        check(rt.lib.yoho_test_attention_bf16(rt.ctx, C.c_void_p(qd.data_ptr()), C.c_void_p(out.data_ptr()), batch, t, heads,
+                                              C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
+        torch.cuda.synchronize()
+    finally:
+        rt.lib.yoho_test_attention_tiles(prev)
+    return out.cpu().numpy(), want
+
+
+@pytest.mark.parametrize("tiles", [0, 2, 3])
+@pytest.mark.parametrize("batch,t,heads", [(1, 128, 1), (2, 100, 2), (1, 1500, 2), (3, 300, 6), (2, 257, 1), (2, 384, 2), (1, 385, 1),
+                                           (1, 513, 3), (1, 64, 1), (1, 1, 1), (1, 1500, 20)])
+def test_tcgen05_attention(rt, batch, t, heads, tiles):
+    rng = np.random.default_rng(batch * 1000 + t + heads)
+    qkv = rng.standard_normal((batch, t, 3, heads, 64)).astype(np.float32)
+    qkv[:, :, 0] *= 2.0                                                  # sharper softmax
+    got, want = _attention_case(rt, qkv, tiles)
     assert np.isfinite(got).all()
     assert np.abs(got - want).max() <= 1.5e-2 * np.abs(want).max()       # P and the output are rounded to bf16
+
+
+@pytest.mark.parametrize("tiles", [2, 3])
+def test_tcgen05_attention_growing_maximum(rt, tiles):
+    """Scores that grow along the first half of the keys and fall along the second: the running maximum rises by more than
+    2^8 from one 64-key step to the next, so the lazy rescaling of O and of the row sum runs in every step up to the
+    middle; after it the exp2 arguments fall below -126 (the clamp of the polynomial exp2); the last step is ragged
+    (1500 = 23 * 64 + 28)."""
+    rng = np.random.default_rng(7)
+    batch, t, heads = 2, 1500, 2
+    qkv = rng.standard_normal((batch, t, 3, heads, 64)).astype(np.float32)
+    ramp = 10.0 - np.abs(np.linspace(-9.8, 9.8, t, dtype=np.float32))          # 0.2 -> 10 at the middle key -> 0.2
+    qkv[:, :, 0] = np.abs(qkv[:, :, 0]) * 1.5                                  # queries: every component positive
+    qkv[:, :, 1] = qkv[:, :, 1] * 0.3 + ramp[None, :, None, None]              # keys: score / 8 ~ 9.6 * ramp (138 log2 units at the peak)
+    got, want = _attention_case(rt, qkv, tiles)
+    assert np.isfinite(got).all()
+    assert np.abs(got - want).max() <= 1.5e-2 * np.abs(want).max()
+
+
+def test_tcgen05_attention_kernels_agree(rt):
+    """Same inputs through the two-tile and the three-tile kernel: both round P to bf16 after the same scaling, so they may
+    differ only by the summation order, the lazy-rescaling points and the polynomial exp2 (7.5e-5 relative)."""
+    rng = np.random.default_rng(11)
+    qkv = rng.standard_normal((2, 700, 3, 3, 64)).astype(np.float32)
+    a, want = _attention_case(rt, qkv, 2)
+    b, _ = _attention_case(rt, qkv, 3)
+    assert np.abs(a - b).max() <= 8e-3 * np.abs(want).max()
 
 
 # ------------------------------------------------------------------ whole encoder

@@ -97,6 +97,7 @@ SIGNATURES = {
     "yoho_test_attention_workspace_bytes": (_sz, [_i, _i, _i]),
     "yoho_test_skinny_gemm": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "yoho_test_attention_bf16": (_i, [_p, _p, _p, _i, _i, _i, _p, _sz, _p]),
+    "yoho_test_attention_tiles": (_i, [_i]),
 }
 
 _lib = None

@@ -365,12 +365,15 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
   if (warp == 9) tmem_dealloc<kAttTmemCols>(tmem_base);
 }
 
+int g_att_tiles_override = 0;   // tests: 0 = by padding, 2 / 3 = that kernel (yoho_test_attention_tiles)
+
 int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16* out, int batch, int t, int heads, cudaStream_t s) {
   if (!qkv || !out) return fail(YOHO_ERR_INVALID, "attention: null operand");
   if (batch <= 0 || t <= 0 || heads <= 0) return YOHO_OK;
   {
     // three-tile kernel (attention3_sm100.cu) when 384-row work items pad the sequence no further than 256-row ones
-    static const int forced = [] { const char* e = getenv("YOHO_ATT_TILES"); return e ? atoi(e) : 0; }();
+    static const int env_forced = [] { const char* e = getenv("YOHO_ATT_TILES"); return e ? atoi(e) : 0; }();
+    const int forced = g_att_tiles_override ? g_att_tiles_override : env_forced;
     const bool pad_ok = ceil_div(t, 384) * 384 <= ceil_div(t, kItemQ) * kItemQ;
     if (forced == 3 || (forced != 2 && pad_ok)) return launch_attention3_bf16(ctx, qkv, out, batch, t, heads, s);
   }
@@ -403,3 +406,10 @@ extern "C" int yoho_debug_att_phases(long long* out16) {
   return int(cudaMemcpyFromSymbol(out16, yoho::g_att_phase, 16 * sizeof(long long)));
 }
 #endif
+
+// test hook: pick the attention kernel (0 = automatic, 2 = two-tile, 3 = three-tile); returns the previous setting
+extern "C" int yoho_test_attention_tiles(int tiles) {
+  const int prev = yoho::g_att_tiles_override;
+  yoho::g_att_tiles_override = (tiles == 2 || tiles == 3) ? tiles : 0;
+  return prev;
+}
