@@ -225,6 +225,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
+      // The accumulator stage goes back to the MMA warp as soon as this warp's LAST chunk of it is in registers, not after
+      // that chunk's math / staging / TMA store; the arrive carries no release fence (the payload is TMEM, ordered by the
+      // tcgen05 fence).  With short K (512-768) the issuer used to wait ~45 % of its time for tmem_empty.
+      const uint32_t empty_remote = mapa_shared(smem_u32(&tmem_empty[as]), 0);   // leader's barrier, both CTAs arrive
+      bool released = false;
+      auto release_acc = [&]() {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster_relaxed(empty_remote);
+        released = true;
+      };
       if (warp_live) {
         if (p.out_is_f32) {
           // 32 fp32 columns (= 128 B rows) per staging buffer
@@ -235,6 +246,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             uint32_t acc[32];
             tmem_ld_32x32b_x32(t_addr + uint32_t(c * 32), acc);
             tmem_ld_wait();
+            if (c + 2 >= BN / 32 || col0 + 64 >= p.n) release_acc();    // warp-uniform: no further chunk for this warp
             float v[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
@@ -264,6 +276,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             tmem_ld_32x32b_x32(t_addr + uint32_t(c * 64), acc0);
             tmem_ld_32x32b_x32(t_addr + uint32_t(c * 64 + 32), acc1);
             tmem_ld_wait();
+            if (c + 2 >= BN / 64 || col0 + 128 >= p.n) release_acc();   // warp-uniform: no further chunk for this warp
             unsigned char* sbuf = my_stage + buf * kStageBufBytes;
             if (lane == 0) tma_store_wait_read<Cfg::kEpiBufs - 1>();
             __syncwarp();
@@ -299,9 +312,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tmem_empty[as]), 0));   // leader's barrier, both CTAs arrive
+      if (!released) release_acc();     // warps without a chunk in this tile
     }
     if (lane == 0) tma_store_wait0();
   }

@@ -128,6 +128,11 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t local_smem_addr, uint32
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// Same without the release fence (no MEMBAR / ERRBAR in front of it): for hand-overs whose payload is not ordinary memory,
+// e.g. a TMEM accumulator that was read with tcgen05.ld + wait::ld and ordered with tcgen05.fence::before_thread_sync.
+__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 // TMA load issued by either CTA of a pair; the completion bytes are signalled on `bar_cluster_addr`, the
 // shared::cluster address of the LEADER CTA's mbarrier (tcgen05 cta_group::2 pipelines).
 __device__ __forceinline__ void tma_load_3d_2sm(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr, int c0, int c1, int c2) {
