@@ -36,7 +36,10 @@ constexpr int kTileQ = 128, kStepKV = 64, kHeadDim = 64;
 constexpr int kItemQ = kTiles * kTileQ;          // 384 query rows per work item
 constexpr int kQBytes = kTileQ * kHeadDim * 2;   // 16 KB
 constexpr int kKvBytes = kStepKV * kHeadDim * 2; // 8 KB
-constexpr int kKvStages = 6;
+#ifndef YOHO_ATT3_KV_STAGES
+#define YOHO_ATT3_KV_STAGES 6
+#endif
+constexpr int kKvStages = YOHO_ATT3_KV_STAGES;
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kTmemS = 0, kTmemO = 64 * kTiles, kTmemP = 128 * kTiles;   // S_t at 64 t, O_t at 192 + 64 t, P_t at 384 + 32 t
 constexpr float kRescaleLog2 = 8.0f;
@@ -97,7 +100,11 @@ __device__ __forceinline__ void exp2_poly_pair(float& lo, float& hi) {
 // every kPolyEvery-th pair of a row takes the polynomial instead of the SFU (0 = none): the SFU is the bound of this
 // kernel (ncu: MUFU queue full for most of the softmax warps' stall samples) while the FMA pipe is ~13 % busy
 constexpr int kPolyEvery = YOHO_ATT_POLY_EVERY;
-__device__ __forceinline__ constexpr bool poly_pair(int i) { return kPolyEvery > 0 && ((i >> 1) % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyEvery - 1; }
+#ifndef YOHO_ATT_POLY_PHASE
+#define YOHO_ATT_POLY_PHASE (YOHO_ATT_POLY_EVERY - 1)
+#endif
+constexpr int kPolyPhase = YOHO_ATT_POLY_PHASE;   // which pair of each group of kPolyEvery
+__device__ __forceinline__ constexpr bool poly_pair(int i) { return kPolyEvery > 0 && ((i >> 1) % (kPolyEvery > 0 ? kPolyEvery : 1)) == kPolyPhase; }
 
 // exp2(s c - mc) of 32 scores -> 16 packed bf16x2 words; returns the sum of the 32 (unrounded) exponentials.
 // Scale / shift and the sum run on packed fp32 pairs (FFMA2 / FADD2); the exponentials are issued one block of 8

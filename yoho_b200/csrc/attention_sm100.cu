@@ -371,10 +371,11 @@ int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16
   if (!qkv || !out) return fail(YOHO_ERR_INVALID, "attention: null operand");
   if (batch <= 0 || t <= 0 || heads <= 0) return YOHO_OK;
   {
-    // three-tile kernel (attention3_sm100.cu) when 384-row work items pad the sequence no further than 256-row ones
+    // Three-tile kernel (attention3_sm100.cu) unless its 384-row work items pad the queries so much further than 256-row
+    // items that the faster kernel loses: cost ~ padded query rows / stand-alone throughput (816 vs 700 TFLOP/s).
     static const int env_forced = [] { const char* e = getenv("YOHO_ATT_TILES"); return e ? atoi(e) : 0; }();
     const int forced = g_att_tiles_override ? g_att_tiles_override : env_forced;
-    const bool pad_ok = ceil_div(t, 384) * 384 <= ceil_div(t, kItemQ) * kItemQ;
+    const bool pad_ok = (long long)ceil_div(t, 384) * 384 * 700 <= (long long)ceil_div(t, kItemQ) * kItemQ * 816;
     if (forced == 3 || (forced != 2 && pad_ok)) return launch_attention3_bf16(ctx, qkv, out, batch, t, heads, s);
   }
   const int dims = heads * kHeadDim;
