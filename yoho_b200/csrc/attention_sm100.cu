@@ -1,6 +1,9 @@
 // Fused self-attention forward for the encoder on tcgen05 tensor cores (sm_100a):
 //   out = softmax(q k^T / sqrt(64)) v   per (clip, head), no mask      (reference whisper.py:52-67)
 // The reference materialises the (B, H, 1500, 1500) score tensor; here scores never leave the SM.
+// This is the two-query-tile kernel.  launch_attention_bf16 (bottom of the file) sends every length whose 384-row
+// padding is acceptable -- 1500, 513, ... -- to the faster three-tile kernel in attention3_sm100.cu and keeps this one
+// for the rest (short sequences, lengths just above a multiple of 384).
 //
 // Persistent kernel, one CTA per SM, 11 warps.  A work item is (clip, head, 256 query rows) = two
 // 128-row query tiles A and B that share every K/V tile; a step is 64 keys of an item:
