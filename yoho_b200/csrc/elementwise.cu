@@ -16,7 +16,7 @@ __device__ __forceinline__ void store4(__nv_bfloat16* p, float4 v) {
 
 // One warp per row.  Reference whisper.py:77,82,134 (flax nn.LayerNorm defaults).
 template <typename OutT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 layernorm_kernel(const float* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ bias,
                  OutT* __restrict__ y, int rows, int dims) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
