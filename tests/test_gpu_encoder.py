@@ -84,7 +84,8 @@ def _attention_case(rt, qkv, tiles):
 
 @pytest.mark.parametrize("tiles", [0, 2, 3])
 @pytest.mark.parametrize("batch,t,heads", [(1, 128, 1), (2, 100, 2), (1, 1500, 2), (3, 300, 6), (2, 257, 1), (2, 384, 2), (1, 385, 1),
-                                           (1, 513, 3), (1, 64, 1), (1, 1, 1), (1, 1500, 20)])
+                                           (1, 513, 3), (1, 64, 1), (1, 1, 1), (1, 1500, 20),
+                                           (40, 130, 4), (50, 60, 4), (9, 400, 20)])   # several work items per CTA, down to one 64-key step each
 def test_tcgen05_attention(rt, batch, t, heads, tiles):
     rng = np.random.default_rng(batch * 1000 + t + heads)
     qkv = rng.standard_normal((batch, t, 3, heads, 64)).astype(np.float32)
