@@ -334,7 +334,7 @@ def stage_attnphases():
     total = sum(ph)
     for n, v in zip(names, ph):
         print(f"[attnphases] {n:32s} {v:10d} clk  {100.0 * v / total:5.1f} %   {v / steps:7.1f} clk/step")
-    mma_names = ["loop top", "wait p_full", "wait o_free / v_full", "issue P V (4 MMA + commits)", "-", "wait s_free + issue Q K^T (g+2)", "-", "-"]
+    mma_names = ["loop top", "wait p_full", "wait o_free / v_full", "issue P V (4 MMA + commits)", "-", "issue Q K^T (g+2)", "-", "-"]
     for n, v in zip(mma_names, list(ph16)[8:]):
         print(f"[attnphases] MMA warp A: {n:32s} {v:10d} clk  {v / steps:7.1f} clk/step")
     print(f"[attnphases] total {total} clk over {items} items / {steps} steps = {total / steps:.0f} clk/step (SFU floor 512 per warp, 1024 per sub-partition)")
