@@ -315,6 +315,7 @@ def stage_attnphases():
     rt = get_runtime()
     lib = rt.lib
     raw = C.CDLL(str(_lib_path()))
+    lib.yoho_test_attention_tiles(2)          # the phase timers live in the two-tile kernel
     batch, t, heads = 64, 1500, 12
     qkv = torch.randn((batch, t, 3, heads, 64), device="cuda")
     out = torch.empty((batch, t, heads * 64), device="cuda")
