@@ -291,6 +291,23 @@ attention3_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
       const int qb = item % p.q_blocks, ch = item / p.q_blocks;
       const int head = ch % p.heads, clip = ch / p.heads;
       float m_ref = -INFINITY, l_run = 0.0f;
+      // Warps whose 32 query rows all lie past the end of the clip (1500 = 3 * 384 + 348: the last warp of the last
+      // item's third tile) only keep the barrier protocol going: their P / O rows are never stored, and tcgen05.mma
+      // rows are independent, so whatever stale bits sit in their TMEM lanes cannot reach a valid row.
+      const bool warp_dead = qb * kItemQ + t * kTileQ + (warp & 3) * 32 >= p.t_len;     // warp-uniform
+      if (warp_dead) {
+        for (int j = 0; j < n_steps; ++j, ++g) {
+          mbar_wait_idle(&sm.s_full[t], g & 1);
+          if (lane == 0) mbar_arrive(&sm.s_free[t]);
+          if (g > 0) mbar_wait_idle(&sm.p_free[t], (g - 1) & 1);
+          if (lane == 0) mbar_arrive(&sm.p_full[t]);
+          __syncwarp();
+        }
+        mbar_wait_idle(&sm.o_last[t], it & 1);
+        if (lane == 0) mbar_arrive(&sm.o_free[t]);
+        __syncwarp();
+        continue;
+      }
       for (int j = 0; j < n_steps; ++j, ++g) {
         mbar_wait_idle(&sm.s_full[t], g & 1);
         tc_fence_after();
@@ -333,7 +350,12 @@ attention3_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
         const uint64_t nmc2 = pack_f32x2(-m_ref * c, -m_ref * c);
         uint32_t packed[32];
         l_run += exp_pack32(a, c2, nmc2, packed);
-        l_run += exp_pack32(b, c2, nmc2, packed + 16);
+        if (j == n_steps - 1 && kv_tail <= 32) {              // CTA-uniform: keys 32-63 of a ragged last step are all masked
+#pragma unroll
+          for (int i = 16; i < 32; ++i) packed[i] = 0u;
+        } else {
+          l_run += exp_pack32(b, c2, nmc2, packed + 16);
+        }
         if (g > 0) {                                          // P_t feeds P V of step g - 1 until that MMA retires (long done)
           mbar_wait(&sm.p_free[t], (g - 1) & 1);
           tc_fence_after();
