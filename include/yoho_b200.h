@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define YOHO_ABI_VERSION 1
+#define YOHO_ABI_VERSION 2
 
 typedef struct yoho_ctx yoho_ctx;               /* per-device immutable state           */
 typedef struct yoho_filterbank yoho_filterbank; /* banded mel filterbank on the device  */
@@ -55,6 +55,11 @@ typedef enum yoho_compute {
   YOHO_COMPUTE_FP32 = 0, /* fp32 operands and accumulation (SIMT), 1e-4 parity path      */
   YOHO_COMPUTE_BF16 = 1  /* bf16 operands, fp32 accumulation on tcgen05 tensor cores     */
 } yoho_compute;
+
+typedef enum yoho_dtype {
+  YOHO_DTYPE_F32 = 0,  /* what the reference returns (float32 everywhere, x64 disabled)           */
+  YOHO_DTYPE_BF16 = 1  /* encoder states rounded once by the final LayerNorm: half the D2H bytes */
+} yoho_dtype;
 
 /* ---- library / context ------------------------------------------------------------- */
 
@@ -152,6 +157,9 @@ typedef struct yoho_enc_desc {
  *     Dense_0.kernel (D,4D), Dense_0.bias (4D), Dense_1.kernel (4D,D), Dense_1.bias (D)
  * Kernels keep the Flax layout (in, out) / (k, in, out). */
 int yoho_encoder_num_tensors(const yoho_enc_desc* desc);
+/* Elements of tensor `idx` in that order (negative yoho_status for a bad desc / index): lets a binding check the
+ * leaves of a parameter pytree against the descriptor before yoho_encoder_weights_pack reads them. */
+long long yoho_encoder_tensor_elems(const yoho_enc_desc* desc, int idx);
 
 size_t yoho_encoder_weights_bytes(const yoho_enc_desc* desc);
 
@@ -169,11 +177,23 @@ size_t yoho_encoder_workspace_bytes(const yoho_enc_desc* desc, int batch, int fr
 
 /* Replaces model.apply({"params": params}, mel, method=Whisper.encode_audio)
  * (whisper.py:194-195, 258) == AudioEncoder.__call__ (whisper.py:124-135).
- *   mel (batch, frames, n_mels) float32  ->  out (batch, T, D) float32
- * yoho_encoder_out_len(frames) must equal desc->seq_len (whisper.py:23 broadcasts). */
-int yoho_encoder_fwd(yoho_ctx* ctx, const yoho_enc_desc* desc, const void* blob, const float* mel,
-                     int batch, int frames, float* out, int compute, void* ws, size_t ws_bytes,
-                     yoho_stream_t stream);
+ *   mel (batch, frames, n_mels) float32  ->  out (batch, T, D) float32 or bf16 (out_dtype: yoho_dtype)
+ * yoho_encoder_out_len(frames) must equal desc->seq_len (whisper.py:23 broadcasts).  blob_bytes is the size of
+ * the packed blob and must be >= yoho_encoder_weights_bytes(desc): a blob packed for another descriptor (another
+ * seq_len moves every offset behind the sinusoid table) is refused instead of being read at wrong offsets.
+ * YOHO_DTYPE_BF16 needs YOHO_COMPUTE_BF16.  The launch sequence only depends on (desc, batch, frames, pointers),
+ * so the call can be captured in a CUDA graph (the Python mirror does so for single-clip latency). */
+int yoho_encoder_fwd(yoho_ctx* ctx, const yoho_enc_desc* desc, const void* blob, size_t blob_bytes,
+                     const float* mel, int batch, int frames, void* out, int out_dtype, int compute,
+                     void* ws, size_t ws_bytes, yoho_stream_t stream);
+
+/* Optional: all-gather of every rank's encoder states for a single consumer (the reference shards a batch over the
+ * devices with common_utils.shard, train/stages/transcription_pretrain_no_voiceprints.py:231-233, and reads results back
+ * per device).  The hot path itself has NO collective.  `nccl_comm` is the caller's ncclComm_t; NCCL is not linked, the
+ * call resolves ncclAllGather from the libnccl already loaded in the process (YOHO_ERR_UNSUPPORTED if there is none).
+ *   states (elems_per_rank) -> gathered (n_ranks * elems_per_rank), rank order; dtype: yoho_dtype. */
+int yoho_allgather_states(yoho_ctx* ctx, void* nccl_comm, const void* states, void* gathered,
+                          size_t elems_per_rank, int dtype, yoho_stream_t stream);
 
 /* ---- cross-attention K/V pre-projection (the step after the path) ------------------------- */
 
@@ -189,6 +209,7 @@ typedef struct yoho_crosskv_desc {
 /* 3 float32 tensors per decoder layer, in order: DecoderBlock_l/MultiHeadAttention_1/key_proj.kernel (d_in, d_out)
  * [no bias, whisper.py:33], value_proj.kernel (d_in, d_out), value_proj.bias (d_out). */
 int yoho_crosskv_num_tensors(const yoho_crosskv_desc* desc);
+long long yoho_crosskv_tensor_elems(const yoho_crosskv_desc* desc, int idx);
 size_t yoho_crosskv_weights_bytes(const yoho_crosskv_desc* desc);
 int yoho_crosskv_weights_pack(yoho_ctx* ctx, const yoho_crosskv_desc* desc, const float* const* tensors,
                               int n_tensors, void* blob, size_t blob_bytes, yoho_stream_t stream);
@@ -223,6 +244,7 @@ typedef struct yoho_decoder_desc {
  *     MultiHeadAttention_1 (cross attention; key/value kernels are (audio_dims, D)): same seven;
  *     LayerNorm_2.{scale,bias};  Dense_0.{kernel (D,4D), bias};  Dense_1.{kernel (4D,D), bias}. */
 int yoho_decoder_num_tensors(const yoho_decoder_desc* desc);
+long long yoho_decoder_tensor_elems(const yoho_decoder_desc* desc, int idx);
 size_t yoho_decoder_weights_bytes(const yoho_decoder_desc* desc);
 int yoho_decoder_weights_pack(yoho_ctx* ctx, const yoho_decoder_desc* desc, const float* const* tensors,
                               int n_tensors, void* blob, size_t blob_bytes, yoho_stream_t stream);
@@ -282,6 +304,7 @@ typedef struct yoho_model_desc {
  *     DenseGeneral_2.kernel (D, kv_heads, 64), Dense_0.kernel (kv_heads*64, D), RMSNorm_1.scale,
  *     SwiGLU Dense_0.kernel (D, 3D), Dense_1.kernel (D, 3D), Dense_2.kernel (3D, D) */
 int yoho_model_num_tensors(const yoho_model_desc* desc);
+long long yoho_model_tensor_elems(const yoho_model_desc* desc, int idx);
 size_t yoho_model_weights_bytes(const yoho_model_desc* desc);
 int yoho_model_weights_pack(yoho_ctx* ctx, const yoho_model_desc* desc, const float* const* tensors,
                             int n_tensors, void* blob, size_t blob_bytes, yoho_stream_t stream);

@@ -279,3 +279,107 @@ def test_encoder_properties_at_bench_size(rt):
     assert float((out[:2] - ref).abs().max() / ref.abs().max()) <= TOL_BF16
     # distinct clips give distinct states (the batch is not collapsing onto one clip)
     assert float((out[0] - out[1]).abs().max()) > 1e-3
+
+
+# ------------------------------------------------------------------ binding hygiene
+def test_one_pytree_at_two_clip_lengths(rt):
+    """The packed blob embeds the sinusoid table (seq_len x D) in front of the layer weights: the same params object used
+    at two clip lengths must get two blobs (the cache key holds the descriptor), and each result must match the oracle."""
+    from oracle import encoder as eo
+    from yoho_b200.nn import AudioEncoder, init_encoder_params
+    params = init_encoder_params(80, 128, 2, seed=9)
+    rng = np.random.default_rng(0)
+    for frames in (199, 61, 199):
+        mel = rng.standard_normal((2, frames, 80)).astype(np.float32)
+        T = (frames + 2 - 3) // 2 + 1
+        got = AudioEncoder(T, 128, 2, 2).apply({"params": params}, mel, compute="fp32")
+        want = eo.audio_encoder(params, mel, 2, np.float64)
+        assert np.abs(got - want).max() <= TOL_FP32
+
+
+def test_wrong_leaf_shape_is_refused(rt):
+    """A leaf whose element count differs from what the descriptor implies is refused before the library reads it."""
+    from yoho_b200.nn import AudioEncoder, init_encoder_params
+    params = init_encoder_params(80, 128, 2, seed=9)
+    params["EncoderBlock_1"]["Dense_0"]["kernel"] = params["EncoderBlock_1"]["Dense_0"]["kernel"][:, :-1]
+    with pytest.raises(ValueError, match="elements"):
+        AudioEncoder(100, 128, 2, 2).apply({"params": params}, np.zeros((1, 199, 80), np.float32))
+
+
+def test_blob_of_another_descriptor_is_refused(rt):
+    import torch
+    from yoho_b200._lib import EncDesc, YohoError, check
+    small, big = EncDesc(80, 128, 2, 1, 100), EncDesc(80, 128, 2, 2, 100)
+    nbytes = rt.lib.yoho_encoder_weights_bytes(C.byref(small))
+    blob = torch.zeros(nbytes + 1024, dtype=torch.uint8, device="cuda")
+    mel = torch.zeros((1, 199, 80), device="cuda")
+    out = torch.zeros((1, 100, 128), device="cuda")
+    ws_bytes = rt.lib.yoho_encoder_workspace_bytes(C.byref(big), 1, 199, 1)
+    ws = rt.workspace("test", ws_bytes)
+    with pytest.raises(YohoError, match="blob"):
+        check(rt.lib.yoho_encoder_fwd(rt.ctx, C.byref(big), C.c_void_p(rt.aligned_ptr(blob)), rt.blob_bytes(blob), C.c_void_p(mel.data_ptr()),
+                                      1, 199, C.c_void_p(out.data_ptr()), 0, 1, C.c_void_p(rt.aligned_ptr(ws)), ws_bytes, rt.stream_ptr()))
+
+
+def test_empty_batch_is_a_no_op(rt):
+    import torch
+    from yoho_b200.nn import init_encoder_params
+    from yoho_b200.pipeline import ClipEncoder
+    from yoho_b200.preprocessing import log_mel_spectogram_chunked
+    enc = ClipEncoder((80, 128, 2, 2), init_encoder_params(80, 128, 2, seed=5), n_samples=32000)
+    out = enc.encode_host(torch.empty((0, 32000), dtype=torch.float32))
+    assert tuple(out.shape) == (0, enc.seq_len, 128)
+    assert tuple(enc.encode(torch.empty((0, 32000), device="cuda")).shape) == (0, enc.seq_len, 128)
+    assert log_mel_spectogram_chunked(np.zeros(0, np.float32), clip_samples=32000).shape == (0, 199, 80)
+
+
+def test_ctx_create_keeps_the_current_device(rt):
+    """yoho_ctx_create / yoho_filterbank_create allocate on their own device and put the caller's device back."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two devices")
+    from yoho_b200.runtime import get_runtime
+    torch.cuda.set_device(0)
+    get_runtime(1)
+    assert torch.cuda.current_device() == 0
+
+
+def test_graph_replay_matches_plain_launches(rt):
+    """BASELINE configs[0] geometry (whisper-tiny, one clip): the CUDA-graph replay of the launch sequence returns exactly
+    what the plain launches do, also after the input buffer was refilled in place."""
+    import torch
+    from yoho_b200.nn import init_encoder_params
+    from yoho_b200.pipeline import ClipEncoder
+    from yoho_b200.synth import synth_batch
+    enc = ClipEncoder("tiny", init_encoder_params(80, 384, 4, seed=42))
+    pcm = torch.from_numpy(synth_batch(1, 480000)).cuda()
+    plain = enc.encode(pcm).clone()
+    out = torch.empty_like(plain)
+    assert torch.equal(enc.encode_graphed(pcm, out), plain)
+    pcm.copy_(torch.from_numpy(synth_batch(1, 480000, first_index=5)).cuda())
+    plain2 = enc.encode(pcm).clone()
+    assert not torch.equal(plain2, plain)
+    assert torch.equal(enc.encode_graphed(pcm, out), plain2)
+
+
+def test_allgather_states_c_abi(rt):
+    """yoho_allgather_states resolves ncclAllGather from the libnccl already in the process (torch's) and runs it on the
+    caller's communicator: here a one-rank communicator built through ctypes, for which the gather is the identity.  The
+    multi-rank gather is measured by bench.py under torchrun (``allgather`` key) through torch.distributed."""
+    import torch
+    from yoho_b200._lib import check
+    nccl = C.CDLL("libnccl.so.2")
+    comm = C.c_void_p()
+    devs = (C.c_int * 1)(torch.cuda.current_device())
+    assert nccl.ncclCommInitAll(C.byref(comm), 1, devs) == 0
+    try:
+        for dtype, code in ((torch.float32, 0), (torch.bfloat16, 1)):
+            states = torch.randn((3, 50, 64), device="cuda").to(dtype)
+            out = torch.zeros_like(states)
+            check(rt.lib.yoho_allgather_states(rt.ctx, comm, C.c_void_p(states.data_ptr()), C.c_void_p(out.data_ptr()),
+                                               states.numel(), code, rt.stream_ptr()))
+            torch.cuda.synchronize()
+            assert torch.equal(out, states)
+    finally:
+        nccl.ncclCommDestroy.argtypes = [C.c_void_p]
+        nccl.ncclCommDestroy(comm)

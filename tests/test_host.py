@@ -17,7 +17,7 @@ ROOT = Path(__file__).resolve().parents[1]
 def test_library_exports_every_declared_symbol(built_library):
     header = (ROOT / "include" / "yoho_b200.h").read_text()
     declared = set(re.findall(r"\b(yoho_[a-z0-9_]+)\s*\(", header))
-    declared -= {"yoho_status", "yoho_norm", "yoho_compute"}
+    declared -= {"yoho_status", "yoho_norm", "yoho_compute", "yoho_dtype"}
     assert len(declared) >= 20
     lib = C.CDLL(str(built_library))
     for name in sorted(declared):
@@ -58,6 +58,19 @@ def test_flatten_order_matches_header():
     assert np.array_equal(o["EncoderBlock_2"]["Dense_1"]["kernel"], p["EncoderBlock_2"]["Dense_1"]["kernel"])
     with pytest.raises(KeyError):
         flatten_encoder_params({k: v for k, v in p.items() if k != "Conv_1"}, 3, flat[4])
+    # the element counts a binding checks before packing (yoho_encoder_tensor_elems) are those of the flattened leaves
+    from yoho_b200 import _lib
+    lib, d = _lib.load(), _lib.EncDesc(80, 128, 2, 3, 100)
+    assert [lib.yoho_encoder_tensor_elems(C.byref(d), i) for i in range(len(flat))] == [int(np.prod(a.shape)) for a in flat]
+    assert lib.yoho_encoder_tensor_elems(C.byref(d), len(flat)) < 0
+
+
+def test_allgather_states_argument_checks(built_library):
+    """No GPU, no communicator: the optional gather entry point refuses null arguments and unknown dtypes."""
+    from yoho_b200 import _lib
+    lib = _lib.load()
+    assert lib.yoho_allgather_states(None, None, None, None, 16, 0, None) == -1
+    assert b"null" in lib.yoho_last_error()
 
 
 def test_product_filterbank_and_table_are_bit_exact(golden_dir):

@@ -13,6 +13,8 @@ LIB_PATH = Path(os.environ.get("YOHO_B200_LIB") or (Path(__file__).resolve().par
 YOHO_OK = 0
 NORM_NONE, NORM_REFERENCE, NORM_WHISPER = 0, 1, 2
 COMPUTE_FP32, COMPUTE_BF16 = 0, 1
+DTYPE_F32, DTYPE_BF16 = 0, 1
+ABI_VERSION = 2
 
 
 class YohoError(RuntimeError):
@@ -65,13 +67,17 @@ SIGNATURES = {
     "yoho_encoder_weights_pack": (_i, [_p, C.POINTER(EncDesc), C.POINTER(_p), _i, _p, _sz, _p]),
     "yoho_encoder_out_len": (_i, [_i]),
     "yoho_encoder_workspace_bytes": (_sz, [C.POINTER(EncDesc), _i, _i, _i]),
-    "yoho_encoder_fwd": (_i, [_p, C.POINTER(EncDesc), _p, _p, _i, _i, _p, _i, _p, _sz, _p]),
+    "yoho_encoder_tensor_elems": (C.c_longlong, [C.POINTER(EncDesc), _i]),
+    "yoho_encoder_fwd": (_i, [_p, C.POINTER(EncDesc), _p, _sz, _p, _i, _i, _p, _i, _i, _p, _sz, _p]),
+    "yoho_allgather_states": (_i, [_p, _p, _p, _p, _sz, _i, _p]),
     "yoho_crosskv_num_tensors": (_i, [C.POINTER(CrossKvDesc)]),
+    "yoho_crosskv_tensor_elems": (C.c_longlong, [C.POINTER(CrossKvDesc), _i]),
     "yoho_crosskv_weights_bytes": (_sz, [C.POINTER(CrossKvDesc)]),
     "yoho_crosskv_weights_pack": (_i, [_p, C.POINTER(CrossKvDesc), C.POINTER(_p), _i, _p, _sz, _p]),
     "yoho_crosskv_workspace_bytes": (_sz, [C.POINTER(CrossKvDesc), _i, _i, _i]),
     "yoho_crosskv_fwd": (_i, [_p, C.POINTER(CrossKvDesc), _p, _p, _i, _i, _p, _i, _p, _sz, _p]),
     "yoho_decoder_num_tensors": (_i, [C.POINTER(DecoderDesc)]),
+    "yoho_decoder_tensor_elems": (C.c_longlong, [C.POINTER(DecoderDesc), _i]),
     "yoho_decoder_weights_bytes": (_sz, [C.POINTER(DecoderDesc)]),
     "yoho_decoder_weights_pack": (_i, [_p, C.POINTER(DecoderDesc), C.POINTER(_p), _i, _p, _sz, _p]),
     "yoho_decoder_workspace_bytes": (_sz, [C.POINTER(DecoderDesc), _i, _i]),
@@ -82,6 +88,7 @@ SIGNATURES = {
     "yoho_decoder_step": (_i, [_p, C.POINTER(DecoderDesc), _p, _p, _i, _p, _sz, _p, _p, _i, _p, _sz, _p]),
     "yoho_decoder_generate": (_i, [_p, C.POINTER(DecoderDesc), _p, _p, _i, _p, _sz, _p, _i, _i, _p, _sz, _p]),
     "yoho_model_num_tensors": (_i, [C.POINTER(ModelDesc)]),
+    "yoho_model_tensor_elems": (C.c_longlong, [C.POINTER(ModelDesc), _i]),
     "yoho_model_weights_bytes": (_sz, [C.POINTER(ModelDesc)]),
     "yoho_model_weights_pack": (_i, [_p, C.POINTER(ModelDesc), C.POINTER(_p), _i, _p, _sz, _p]),
     "yoho_model_out_len": (_i, [_i]),
@@ -117,8 +124,8 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)          # AttributeError here == header / library mismatch
         fn.restype = res
         fn.argtypes = args
-    if lib.yoho_abi_version() != 1:
-        raise ImportError(f"libyoho_b200 ABI {lib.yoho_abi_version()} != 1")
+    if lib.yoho_abi_version() != ABI_VERSION:
+        raise ImportError(f"libyoho_b200 ABI {lib.yoho_abi_version()} != {ABI_VERSION}: rebuild with `python -m yoho_b200.build --force`")
     _lib = lib
     return lib
 

@@ -67,7 +67,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as pool:
         objs = list(pool.map(compile_one, SOURCES))
     link = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(LIB), *map(str, objs),
-            "-cudart", "static", "-Xlinker", "--exclude-libs=ALL"]
+            "-cudart", "static", "-Xlinker", "--exclude-libs=ALL", "-ldl"]
     r = subprocess.run(link, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

@@ -1,6 +1,8 @@
 // Context, filterbank and error plumbing of the C ABI (include/yoho_b200.h).
 #include "common.cuh"
 
+#include <dlfcn.h>
+
 #include <atomic>
 #include <cmath>
 #include <mutex>
@@ -62,6 +64,17 @@ ProfScope::~ProfScope() {
   if (slot < int(g_prof_records.size())) cudaEventRecord(g_prof_records[slot].stop, stream);
 }
 
+// Setup calls allocate on a given device: switch to it and put the caller's device back afterwards.
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t error = cudaSuccess;
+  explicit DeviceGuard(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != device) error = cudaSetDevice(device); else prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
 }  // namespace yoho
 
 using namespace yoho;
@@ -107,7 +120,8 @@ extern "C" int yoho_ctx_create(int device, yoho_ctx** out) {
   int count = 0;
   YOHO_CUDA_CHECK(cudaGetDeviceCount(&count));
   if (device < 0 || device >= count) return fail(YOHO_ERR_INVALID, "yoho_ctx_create: device %d of %d", device, count);
-  YOHO_CUDA_CHECK(cudaSetDevice(device));
+  DeviceGuard guard(device);                        // the caller's current device is restored on every return path
+  if (guard.error != cudaSuccess) return fail(YOHO_ERR_CUDA, "yoho_ctx_create: cudaSetDevice(%d): %s", device, cudaGetErrorString(guard.error));
   cudaDeviceProp prop;
   YOHO_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
   if (prop.major != 10)
@@ -170,7 +184,8 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
   if (!ctx || !host_filters || !out) return fail(YOHO_ERR_INVALID, "yoho_filterbank_create: null argument");
   *out = nullptr;
   if (n_mels <= 0 || n_bins <= 0) return fail(YOHO_ERR_INVALID, "yoho_filterbank_create: shape (%d, %d)", n_mels, n_bins);
-  YOHO_CUDA_CHECK(cudaSetDevice(ctx->device));
+  DeviceGuard guard(ctx->device);
+  if (guard.error != cudaSuccess) return fail(YOHO_ERR_CUDA, "yoho_filterbank_create: cudaSetDevice(%d): %s", ctx->device, cudaGetErrorString(guard.error));
   if (n_mels > kMelWarps * kMelMaxRounds) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: n_mels=%d > %d", n_mels, kMelWarps * kMelMaxRounds);
   if (n_bins > kMelPRows) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: n_bins=%d > %d", n_bins, kMelPRows);
   std::vector<int> lo(n_mels, 0), len(n_mels, 0);
@@ -229,5 +244,35 @@ extern "C" int yoho_filterbank_destroy(yoho_filterbank* fb) {
   if (fb->d_bands) cudaFree(fb->d_bands);
   if (fb->d_weights) cudaFree(fb->d_weights);
   delete fb;
+  return YOHO_OK;
+}
+
+// ---- optional gather of encoder states -------------------------------------------------------------
+// NCCL is not linked: the symbol is taken from the libnccl the host process already uses (torch's, or the JAX
+// runtime's), so the communicator handed in and the function called belong to the same library instance.
+extern "C" int yoho_allgather_states(yoho_ctx* ctx, void* nccl_comm, const void* states, void* gathered,
+                                     size_t elems_per_rank, int dtype, yoho_stream_t stream) {
+  if (!ctx || !nccl_comm || !states || !gathered) return fail(YOHO_ERR_INVALID, "yoho_allgather_states: null argument");
+  if (dtype != YOHO_DTYPE_F32 && dtype != YOHO_DTYPE_BF16) return fail(YOHO_ERR_INVALID, "yoho_allgather_states: dtype=%d", dtype);
+  using AllGatherFn = int (*)(const void*, void*, size_t, int, void*, cudaStream_t);
+  static AllGatherFn fn = nullptr;
+  static std::mutex mu;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!fn) {
+      void* sym = dlsym(RTLD_DEFAULT, "ncclAllGather");
+      for (const char* name : {"libnccl.so.2", "libnccl.so"}) {
+        if (sym) break;
+        void* h = dlopen(name, RTLD_LAZY | RTLD_NOLOAD);
+        if (!h) h = dlopen(name, RTLD_LAZY);
+        if (h) sym = dlsym(h, "ncclAllGather");
+      }
+      if (!sym) return fail(YOHO_ERR_UNSUPPORTED, "yoho_allgather_states: no ncclAllGather in this process (load libnccl.so.2 first)");
+      fn = reinterpret_cast<AllGatherFn>(sym);
+    }
+  }
+  const int nccl_dtype = dtype == YOHO_DTYPE_F32 ? 7 /* ncclFloat32 */ : 9 /* ncclBfloat16 */;
+  const int rc = fn(states, gathered, elems_per_rank, nccl_dtype, nccl_comm, static_cast<cudaStream_t>(stream));
+  if (rc != 0) return fail(YOHO_ERR_CUDA, "yoho_allgather_states: ncclAllGather returned %d", rc);
   return YOHO_OK;
 }

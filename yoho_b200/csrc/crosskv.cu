@@ -47,6 +47,12 @@ extern "C" int yoho_crosskv_num_tensors(const yoho_crosskv_desc* desc) {
   return 3 * desc->n_layers;
 }
 
+extern "C" long long yoho_crosskv_tensor_elems(const yoho_crosskv_desc* desc, int idx) {
+  if (ckv_check(desc, "yoho_crosskv_tensor_elems") != YOHO_OK) return YOHO_ERR_INVALID;
+  if (idx < 0 || idx >= 3 * desc->n_layers) return fail(YOHO_ERR_INVALID, "yoho_crosskv_tensor_elems: index %d", idx);
+  return idx % 3 == 2 ? (long long)desc->d_out : (long long)desc->d_in * desc->d_out;
+}
+
 extern "C" size_t yoho_crosskv_weights_bytes(const yoho_crosskv_desc* desc) {
   if (ckv_check(desc, "yoho_crosskv_weights_bytes") != YOHO_OK) return 0;
   return ckv_layer_bytes(*desc, nullptr) * size_t(desc->n_layers) + 1024;

@@ -346,6 +346,12 @@ extern "C" int yoho_decoder_num_tensors(const yoho_decoder_desc* desc) {
   return kDecFixed + kDecPerLayer * desc->n_layers;
 }
 
+extern "C" long long yoho_decoder_tensor_elems(const yoho_decoder_desc* desc, int idx) {
+  if (dec_check(desc, "yoho_decoder_tensor_elems") != YOHO_OK) return YOHO_ERR_INVALID;
+  if (idx < 0 || idx >= kDecFixed + kDecPerLayer * desc->n_layers) return fail(YOHO_ERR_INVALID, "yoho_decoder_tensor_elems: index %d", idx);
+  return (long long)dec_tensor_elems(*desc, idx);
+}
+
 extern "C" size_t yoho_decoder_weights_bytes(const yoho_decoder_desc* desc) {
   if (dec_check(desc, "yoho_decoder_weights_bytes") != YOHO_OK) return 0;
   return dec_plan_blob(*desc).total;

@@ -139,7 +139,7 @@ static WsPlan plan_ws(const yoho_enc_desc& d, int batch, int frames, int compute
 #define YOHO_TRY(expr) do { int _r = (expr); if (_r != YOHO_OK) return _r; } while (0)
 
 static int forward_bf16(yoho_ctx* ctx, const yoho_enc_desc& d, const BlobLayout& L, const char* blob, const float* mel,
-                        int batch, int frames, float* out, char* ws, const WsPlan& w, cudaStream_t s) {
+                        int batch, int frames, void* out, int out_dtype, char* ws, const WsPlan& w, cudaStream_t s) {
   using bf = __nv_bfloat16;
   const int T = conv_out_len(frames), D = d.dims, Fp = 2 * T, K0 = conv0_k(d.n_mels);
   const int rows = batch * T;
@@ -211,8 +211,9 @@ static int forward_bf16(yoho_ctx* ctx, const yoho_enc_desc& d, const BlobLayout&
       YOHO_TRY(launch_gemm_bf16(ctx, g, s));
     }
   }
-  // final LayerNorm (whisper.py:134)
-  return launch_layernorm_f32(x, F32(L.lnf_s), F32(L.lnf_b), out, rows, D, s);
+  // final LayerNorm (whisper.py:134); bf16 states are rounded here, once
+  if (out_dtype == YOHO_DTYPE_BF16) return launch_layernorm_bf16(x, F32(L.lnf_s), F32(L.lnf_b), static_cast<bf*>(out), rows, D, s);
+  return launch_layernorm_f32(x, F32(L.lnf_s), F32(L.lnf_b), static_cast<float*>(out), rows, D, s);
 }
 
 // ------------------------------------------------------------------------------ forward, fp32
@@ -291,6 +292,12 @@ extern "C" int yoho_encoder_num_tensors(const yoho_enc_desc* desc) {
   return kTensorsFixed + kTensorsPerLayer * desc->n_layers;
 }
 
+extern "C" long long yoho_encoder_tensor_elems(const yoho_enc_desc* desc, int idx) {
+  if (check_desc(desc, "yoho_encoder_tensor_elems") != YOHO_OK) return YOHO_ERR_INVALID;
+  if (idx < 0 || idx >= kTensorsFixed + kTensorsPerLayer * desc->n_layers) return fail(YOHO_ERR_INVALID, "yoho_encoder_tensor_elems: index %d", idx);
+  return (long long)tensor_elems(*desc, idx);
+}
+
 extern "C" size_t yoho_encoder_weights_bytes(const yoho_enc_desc* desc) {
   if (check_desc(desc, "yoho_encoder_weights_bytes") != YOHO_OK) return 0;
   return plan_blob(*desc).total;
@@ -354,13 +361,17 @@ extern "C" size_t yoho_encoder_workspace_bytes(const yoho_enc_desc* desc, int ba
   return plan_ws(*desc, batch, frames, compute).total;
 }
 
-extern "C" int yoho_encoder_fwd(yoho_ctx* ctx, const yoho_enc_desc* desc, const void* blob, const float* mel, int batch,
-                                int frames, float* out, int compute, void* ws, size_t ws_bytes, yoho_stream_t stream_) {
+extern "C" int yoho_encoder_fwd(yoho_ctx* ctx, const yoho_enc_desc* desc, const void* blob, size_t blob_bytes, const float* mel,
+                                int batch, int frames, void* out, int out_dtype, int compute, void* ws, size_t ws_bytes,
+                                yoho_stream_t stream_) {
   cudaStream_t s = static_cast<cudaStream_t>(stream_);
   if (!ctx || !blob || !mel || !out) return fail(YOHO_ERR_INVALID, "yoho_encoder_fwd: null argument");
   YOHO_TRY(check_desc(desc, "yoho_encoder_fwd"));
   if (ctx->cc_major != 10) return fail(YOHO_ERR_ARCH, "yoho_encoder_fwd: device is sm_%d%d, kernels are sm_100a only", ctx->cc_major, ctx->cc_minor);
   if (compute != YOHO_COMPUTE_FP32 && compute != YOHO_COMPUTE_BF16) return fail(YOHO_ERR_INVALID, "yoho_encoder_fwd: compute=%d", compute);
+  if (out_dtype != YOHO_DTYPE_F32 && out_dtype != YOHO_DTYPE_BF16) return fail(YOHO_ERR_INVALID, "yoho_encoder_fwd: out_dtype=%d", out_dtype);
+  if (out_dtype == YOHO_DTYPE_BF16 && compute != YOHO_COMPUTE_BF16)
+    return fail(YOHO_ERR_UNSUPPORTED, "yoho_encoder_fwd: bf16 states are produced by the bf16 compute path only");
   if (batch < 0 || frames <= 0) return fail(YOHO_ERR_INVALID, "yoho_encoder_fwd: batch=%d frames=%d", batch, frames);
   const int T = conv_out_len(frames);
   if (T != desc->seq_len)
@@ -372,9 +383,11 @@ extern "C" int yoho_encoder_fwd(yoho_ctx* ctx, const yoho_enc_desc* desc, const 
   if (reinterpret_cast<uintptr_t>(ws) % 1024 != 0 || reinterpret_cast<uintptr_t>(blob) % 256 != 0)
     return fail(YOHO_ERR_INVALID, "yoho_encoder_fwd: workspace must be 1024-byte and blob 256-byte aligned");
   BlobLayout L = plan_blob(*desc);
+  if (blob_bytes < L.total)
+    return fail(YOHO_ERR_WORKSPACE, "yoho_encoder_fwd: blob of %zu bytes, this descriptor's layout needs %zu (packed for another shape?)", blob_bytes, L.total);
   if (compute == YOHO_COMPUTE_BF16)
-    return forward_bf16(ctx, *desc, L, static_cast<const char*>(blob), mel, batch, frames, out, static_cast<char*>(ws), w, s);
-  return forward_fp32(*desc, L, static_cast<const char*>(blob), mel, batch, frames, out, static_cast<char*>(ws), w, s);
+    return forward_bf16(ctx, *desc, L, static_cast<const char*>(blob), mel, batch, frames, out, out_dtype, static_cast<char*>(ws), w, s);
+  return forward_fp32(*desc, L, static_cast<const char*>(blob), mel, batch, frames, static_cast<float*>(out), static_cast<char*>(ws), w, s);
 }
 
 // ------------------------------------------------------------------------------ test hooks

@@ -447,6 +447,7 @@ template <typename T>
 static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm, int batch, int n_samples, long long total_samples,
                          int n_fft, int hop, float* out, int norm, void* ws, size_t ws_bytes,
                          cudaStream_t stream) {
+  if (batch == 0 && ctx && fb) return YOHO_OK;      // an empty batch / recording has no buffers to point at
   if (!ctx || !fb || !pcm || !out) return fail(YOHO_ERR_INVALID, "yoho_logmel: null argument");
   if (ctx->cc_major != 10) return fail(YOHO_ERR_ARCH, "yoho_logmel: device %d is sm_%d%d, kernels are sm_100a only", ctx->device, ctx->cc_major, ctx->cc_minor);
   if (batch < 0 || n_samples <= 0) return fail(YOHO_ERR_INVALID, "yoho_logmel: batch=%d n_samples=%d", batch, n_samples);

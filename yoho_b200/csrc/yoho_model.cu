@@ -288,6 +288,12 @@ extern "C" int yoho_model_num_tensors(const yoho_model_desc* desc) {
   return kYmFixed + kYmPerBlock * desc->n_blocks;
 }
 
+extern "C" long long yoho_model_tensor_elems(const yoho_model_desc* desc, int idx) {
+  if (ym_check_desc(desc, "yoho_model_tensor_elems") != YOHO_OK) return YOHO_ERR_INVALID;
+  if (idx < 0 || idx >= kYmFixed + kYmPerBlock * desc->n_blocks) return fail(YOHO_ERR_INVALID, "yoho_model_tensor_elems: index %d", idx);
+  return (long long)ym_tensor_elems(*desc, idx);
+}
+
 extern "C" size_t yoho_model_weights_bytes(const yoho_model_desc* desc) {
   if (ym_check_desc(desc, "yoho_model_weights_bytes") != YOHO_OK) return 0;
   return ym_plan_blob(*desc).total;

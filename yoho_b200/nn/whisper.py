@@ -22,7 +22,7 @@ from dataclasses import dataclass
 import numpy as np
 import torch
 
-from .._lib import COMPUTE_BF16, COMPUTE_FP32, CrossKvDesc, DecoderDesc, EncDesc, check
+from .._lib import COMPUTE_BF16, COMPUTE_FP32, DTYPE_BF16, DTYPE_F32, CrossKvDesc, DecoderDesc, EncDesc, check
 from ..runtime import get_runtime
 
 _COMPUTE = {"bf16": COMPUTE_BF16, "fp32": COMPUTE_FP32, COMPUTE_BF16: COMPUTE_BF16, COMPUTE_FP32: COMPUTE_FP32}
@@ -152,9 +152,10 @@ class AudioEncoder:
         ws_bytes = rt.lib.yoho_encoder_workspace_bytes(C.byref(desc), B, F, mode)
         ws = rt.workspace("encoder", ws_bytes)
         with torch.cuda.device(rt.device):
-            check(rt.lib.yoho_encoder_fwd(rt.ctx, C.byref(desc), C.c_void_p(rt.aligned_ptr(blob)), C.c_void_p(x.data_ptr()),
-                                          B, F, C.c_void_p(out.data_ptr()), mode, C.c_void_p(rt.aligned_ptr(ws)), ws_bytes,
-                                          rt.stream_ptr()))
+            check(rt.lib.yoho_encoder_fwd(rt.ctx, C.byref(desc), C.c_void_p(rt.aligned_ptr(blob)), rt.blob_bytes(blob),
+                                          C.c_void_p(x.data_ptr()), B, F, C.c_void_p(out.data_ptr()),
+                                          DTYPE_BF16 if out.dtype == torch.bfloat16 else DTYPE_F32, mode,
+                                          C.c_void_p(rt.aligned_ptr(ws)), ws_bytes, rt.stream_ptr()))
         return out.cpu().numpy() if host else out
 
 

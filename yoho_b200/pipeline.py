@@ -16,13 +16,15 @@ import numpy as np
 import torch
 
 from . import MODEL_SHAPES
-from ._lib import COMPUTE_BF16, COMPUTE_FP32, NORM_NONE, NORM_REFERENCE, NORM_WHISPER, EncDesc, check
+from ._lib import COMPUTE_BF16, COMPUTE_FP32, DTYPE_BF16, DTYPE_F32, NORM_NONE, NORM_REFERENCE, NORM_WHISPER, EncDesc, check
 from .nn.whisper import conv_out_len, flatten_encoder_params, sin_positional_encoding
 from .preprocessing.mel_filterbanks import mel_filter_banks
 from .runtime import get_runtime
 
 _NORM = {"none": NORM_NONE, "reference": NORM_REFERENCE, "whisper": NORM_WHISPER}
 _COMPUTE = {"bf16": COMPUTE_BF16, "fp32": COMPUTE_FP32}
+_STATES = {"fp32": torch.float32, "float32": torch.float32, "bf16": torch.bfloat16, "bfloat16": torch.bfloat16,
+           torch.float32: torch.float32, torch.bfloat16: torch.bfloat16}
 
 
 def chunk_plan(batch: int, chunk: int, taper: bool = True) -> list[tuple[int, int]]:
@@ -53,7 +55,8 @@ class ClipEncoder:
     """
 
     def __init__(self, model, params: dict, n_samples: int = 480000, norm: str = "reference", compute: str = "bf16",
-                 sample_rate: int = 16000, n_fft: int = 400, hop: int = 160, device: int | None = None):
+                 sample_rate: int = 16000, n_fft: int = 400, hop: int = 160, device: int | None = None,
+                 states_dtype="fp32"):
         shape = MODEL_SHAPES[model] if isinstance(model, str) else tuple(model)
         self.n_mels, self.dims, self.n_heads, self.n_layers = shape
         self.rt = get_runtime(device)
@@ -62,6 +65,11 @@ class ClipEncoder:
         self.frames = check(lib.yoho_stft_frames(self.n_samples, n_fft, hop))
         self.seq_len = conv_out_len(self.frames)
         self.norm, self.compute = _NORM[norm], _COMPUTE[compute]
+        # dtype of the encoder states handed back: float32 is what the reference returns; bfloat16 (rounded once, by the
+        # final LayerNorm) halves the D2H bytes of the host-facing path
+        self.states_dtype = _STATES[states_dtype]
+        if self.states_dtype == torch.bfloat16 and self.compute != COMPUTE_BF16:
+            raise ValueError("bf16 encoder states need compute='bf16'")
         self.fb = self.rt.filterbank(mel_filter_banks(sample_rate, n_fft, self.n_mels))
         params = params.get("params", params)
         params = params.get("audio_encoder", params)
@@ -71,6 +79,7 @@ class ClipEncoder:
         self._mel: dict[int, torch.Tensor] = {}
         self._stage: dict = {}
         self._streams = None
+        self._graphs: dict = {}
 
     # ---- device-resident path -------------------------------------------------------------
     def _mel_buf(self, batch: int, slot: int = 0) -> torch.Tensor:
@@ -100,11 +109,14 @@ class ClipEncoder:
         rt, lib = self.rt, self.rt.lib
         B = mel.shape[0]
         if out is None:
-            out = torch.empty((B, self.seq_len, self.dims), dtype=torch.float32, device=rt.device)
+            out = torch.empty((B, self.seq_len, self.dims), dtype=self.states_dtype, device=rt.device)
+        if out.dtype not in (torch.float32, torch.bfloat16) or not out.is_contiguous():
+            raise ValueError("encoder states go to a contiguous float32 or bfloat16 tensor")
         ws_bytes = lib.yoho_encoder_workspace_bytes(C.byref(self.desc), B, self.frames, self.compute)
         ws = rt.workspace(ws_tag, ws_bytes)
-        check(lib.yoho_encoder_fwd(rt.ctx, C.byref(self.desc), C.c_void_p(rt.aligned_ptr(self.blob)), C.c_void_p(mel.data_ptr()),
-                                   B, self.frames, C.c_void_p(out.data_ptr()), self.compute,
+        check(lib.yoho_encoder_fwd(rt.ctx, C.byref(self.desc), C.c_void_p(rt.aligned_ptr(self.blob)), rt.blob_bytes(self.blob),
+                                   C.c_void_p(mel.data_ptr()), B, self.frames, C.c_void_p(out.data_ptr()),
+                                   DTYPE_BF16 if out.dtype == torch.bfloat16 else DTYPE_F32, self.compute,
                                    C.c_void_p(rt.aligned_ptr(ws)), ws_bytes, rt.stream_ptr()))
         return out
 
@@ -112,13 +124,45 @@ class ClipEncoder:
         """PCM resident in HBM -> encoder states resident in HBM (current stream, no host sync)."""
         B = pcm.shape[0]
         if out is None:
-            out = torch.empty((B, self.seq_len, self.dims), dtype=torch.float32, device=self.rt.device)
+            out = torch.empty((B, self.seq_len, self.dims), dtype=self.states_dtype, device=self.rt.device)
+        if B == 0:
+            return out
         step = B if not chunk_clips else max(1, min(int(chunk_clips), B))
         with torch.cuda.device(self.rt.device):
             for b0 in range(0, B, step):
                 b1 = min(B, b0 + step)
                 mel = self.logmel(pcm[b0:b1], self._mel_buf(b1 - b0))
                 self.encoder(mel, out[b0:b1])
+        return out
+
+    def encode_graphed(self, pcm: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        """``encode`` replayed from a CUDA graph: the launch sequence of the library depends only on (shapes, pointers),
+        so the ~60 launches of a small batch (BASELINE configs[0]: one clip, whisper.py:255-258) cost one graph launch
+        instead of 60 launch latencies.  The graph is captured once per (pcm, out) buffer pair; both must stay alive and
+        the caller refills ``pcm`` in place between calls."""
+        B = pcm.shape[0]
+        if out is None:
+            out = torch.empty((B, self.seq_len, self.dims), dtype=self.states_dtype, device=self.rt.device)
+        if B == 0:
+            return out
+        key = (pcm.data_ptr(), out.data_ptr(), B, pcm.dtype, out.dtype)
+        entry = self._graphs.get(key)
+        if entry is None:
+            with torch.cuda.device(self.rt.device):
+                self._reserve(B)
+                side = torch.cuda.Stream(device=self.rt.device)
+                side.wait_stream(torch.cuda.current_stream(self.rt.device))
+                with torch.cuda.stream(side):
+                    self.encode(pcm, out)                       # warm-up outside the capture (function attributes, workspaces)
+                torch.cuda.current_stream(self.rt.device).wait_stream(side)
+                torch.cuda.synchronize(self.rt.device)
+                graph = torch.cuda.CUDAGraph()
+                n0 = self.rt.lib.yoho_launch_count()
+                with torch.cuda.graph(graph):
+                    self.encode(pcm, out)
+                self.graph_kernels = int(self.rt.lib.yoho_launch_count() - n0)   # kernel nodes replayed per call
+            entry = self._graphs[key] = (graph, pcm, out)
+        entry[0].replay()
         return out
 
     def _reserve(self, batch: int) -> None:
@@ -133,7 +177,7 @@ class ClipEncoder:
     def host_buffers(self, batch: int, pcm_dtype: torch.dtype = torch.float32) -> tuple[torch.Tensor, torch.Tensor]:
         """Pinned host buffers shaped for ``encode_host``: PCM (batch, n_samples) and states (batch, seq_len, dims)."""
         return (torch.empty((batch, self.n_samples), dtype=pcm_dtype, pin_memory=True),
-                torch.empty((batch, self.seq_len, self.dims), dtype=torch.float32, pin_memory=True))
+                torch.empty((batch, self.seq_len, self.dims), dtype=self.states_dtype, pin_memory=True))
 
     def encode_host(self, pcm_host: torch.Tensor, out_host: torch.Tensor | None = None, chunk_clips: int = 64,
                     sync: bool = True, taper: bool = True) -> torch.Tensor:
@@ -144,7 +188,9 @@ class ClipEncoder:
             pcm_host = torch.from_numpy(np.ascontiguousarray(pcm_host))
         B = pcm_host.shape[0]
         if out_host is None:
-            out_host = torch.empty((B, self.seq_len, self.dims), dtype=torch.float32, pin_memory=True)
+            out_host = torch.empty((B, self.seq_len, self.dims), dtype=self.states_dtype, pin_memory=True)
+        if B == 0:                                              # the C ABI treats batch == 0 as a no-op; so does the pipeline
+            return out_host
         dev = self.rt.device
         chunk = max(1, min(int(chunk_clips), (B + 1) // 2))     # at least two chunks, so that copies can hide behind kernels
         self.last_chunk_clips = chunk
@@ -152,11 +198,11 @@ class ClipEncoder:
             if self._streams is None:
                 self._streams = tuple(torch.cuda.Stream(device=dev) for _ in range(3))
             s_in, s_run, s_out = self._streams
-            key = (chunk, pcm_host.dtype)
+            key = (chunk, pcm_host.dtype, out_host.dtype)
             st = self._stage.get(key)
             if st is None:
                 st = {"pcm": [torch.empty((chunk, self.n_samples), dtype=pcm_host.dtype, device=dev) for _ in range(2)],
-                      "out": [torch.empty((chunk, self.seq_len, self.dims), dtype=torch.float32, device=dev) for _ in range(2)]}
+                      "out": [torch.empty((chunk, self.seq_len, self.dims), dtype=out_host.dtype, device=dev) for _ in range(2)]}
                 self._stage = {key: st}
             entry = torch.cuda.current_stream(dev)
             ready = torch.cuda.Event()

@@ -57,6 +57,8 @@ def _logmel(audio, n_fft: int, hop_len: int, sample_rate: int, n_mels: int, norm
     fb = rt.filterbank(mel_filter_banks(sample_rate, n_fft, n_mels))
     if out is None:
         out = torch.empty((B, frames, n_mels), dtype=torch.float32, device=rt.device)
+    if B == 0:
+        return _finish(out, host)
     ws_bytes = rt.lib.yoho_logmel_workspace_bytes(B, N, n_fft, hop_len, n_mels)
     ws = rt.workspace("logmel", ws_bytes)
     fn = rt.lib.yoho_logmel_s16 if int16 else rt.lib.yoho_logmel_f32
@@ -138,6 +140,8 @@ def log_mel_spectogram_chunked(recording, clip_samples: int = 480000, n_fft: int
     fb = rt.filterbank(mel_filter_banks(sample_rate, n_fft, n_mels))
     if out is None:
         out = torch.empty((clips, frames, n_mels), dtype=torch.float32, device=rt.device)
+    if clips == 0:                                      # empty recording: nothing to launch (the C ABI agrees: batch 0 is a no-op)
+        return _finish(out, host)
     ws_bytes = rt.lib.yoho_logmel_workspace_bytes(max(clips, 1), clip_samples, n_fft, hop_len, n_mels)
     ws = rt.workspace("logmel", ws_bytes)
     fn = rt.lib.yoho_logmel_chunked_s16 if int16 else rt.lib.yoho_logmel_chunked_f32

@@ -28,7 +28,8 @@ class Runtime:
         self.lib = _lib.load()
         self.device = torch.device("cuda", device)
         handle = C.c_void_p()
-        check(self.lib.yoho_ctx_create(device, C.byref(handle)))
+        with torch.cuda.device(self.device):       # the library restores the current device as well; belt and braces
+            check(self.lib.yoho_ctx_create(device, C.byref(handle)))
         self.ctx = handle
         self._filterbanks: dict = {}
         self._workspaces: dict[str, torch.Tensor] = {}
@@ -53,6 +54,11 @@ class Runtime:
     def aligned_ptr(buf: torch.Tensor, align: int = 1024) -> int:
         p = buf.data_ptr()
         return (p + align - 1) // align * align
+
+    @classmethod
+    def blob_bytes(cls, blob: torch.Tensor) -> int:
+        """Bytes usable behind ``aligned_ptr(blob)`` (what the ``*_fwd`` entry points check the descriptor's layout against)."""
+        return int(blob.numel() - (cls.aligned_ptr(blob) - blob.data_ptr()))
 
     def pinned(self, tag: str, shape, dtype: torch.dtype) -> torch.Tensor:
         n = int(np.prod(shape))
@@ -94,15 +100,24 @@ class Runtime:
         """Pack (once per params object) the float32 tensors into the device blob the kernels read.
         ``family``: "encoder" (yoho_encoder_*: Whisper AudioEncoder), "model" (yoho_model_*: YOHO's own encoder),
         "crosskv" (yoho_crosskv_*) or "decoder" (yoho_decoder_*: Whisper TextDecoder)."""
-        key = (family, id(params))
+        # the blob layout depends on every desc field (the sinusoid / RoPE table is sized by seq_len and every later
+        # offset follows it), so the descriptor is part of the key: one pytree used at two clip lengths gets two blobs
+        key = (family, id(params), bytes(desc))
         hit = self._weights.get(key)
         if hit is not None and hit[0] is params:
             return hit[1]
         bytes_fn = getattr(self.lib, f"yoho_{family}_weights_bytes")
         pack_fn = getattr(self.lib, f"yoho_{family}_weights_pack")
+        elems_fn = getattr(self.lib, f"yoho_{family}_tensor_elems")
         nbytes = bytes_fn(C.byref(desc))
         if nbytes == 0:
             raise _lib.YohoError(-1, self.lib.yoho_last_error().decode())
+        # the C side copies tensor_elems(desc, i) floats from each pointer: a leaf of another shape would be read past its end
+        for i, t in enumerate(tensors):
+            want, have = int(elems_fn(C.byref(desc), i)), int(np.prod(np.shape(t)))
+            if want != have:
+                raise ValueError(f"{family} weight tensor {i} has {have} elements (shape {tuple(np.shape(t))}); "
+                                 f"the descriptor {[getattr(desc, f) for f, _ in desc._fields_]} needs {want}")
         blob = torch.empty(nbytes + 1024, dtype=torch.uint8, device=self.device)
         keep, ptrs = [], (C.c_void_p * len(tensors))()
         for i, t in enumerate(tensors):
