@@ -168,7 +168,7 @@ def stage_perf():
     for norm in ("none", "reference"):
         ms = timed(lambda: pp.log_mel_spectogram(pcm, norm=norm, out=out))
         gbs = B * 2879680 / ms / 1e6
-        print(f"[perf] frontend B={B} norm={norm}: {ms:.3f} ms  {gbs:.0f} GB/s algorithmic ({gbs / 6540.2 * 100:.1f}% of measured HBM peak)")
+        print(f"[perf] frontend B={B} norm={norm}: {ms:.3f} ms  {gbs:.0f} GB/s algorithmic ({gbs / 6451.5 * 100:.1f}% of measured HBM peak)")
     mel = pp.log_mel_spectogram(pcm, norm="reference")
     for name, (n_mels, dims, heads, layers), b in (("base", (80, 512, 8, 6), 64), ("small", (80, 768, 12, 12), 64)):
         params = init_encoder_params(n_mels, dims, layers, seed=1)
@@ -192,7 +192,32 @@ def stage_logmelperf():
                 ms = timed(lambda: pp.log_mel_spectogram(pcm, n_mels=M, norm=norm, out=out), iters=20, warm=3)
                 gbs = B * (N * pcm.element_size() + F * M * 4) / ms / 1e6
                 print(f"[logmelperf] B={B} N={N} M={M} {name} norm={norm}: {ms:.3f} ms  {gbs:.0f} GB/s algorithmic "
-                      f"({gbs / 6540.2 * 100:.1f}% of measured HBM peak)  {B * N / 16000.0 / ms * 1000:.0f}x realtime")
+                      f"({gbs / 6451.5 * 100:.1f}% of measured HBM peak)  {B * N / 16000.0 / ms * 1000:.0f}x realtime")
+
+
+def stage_logmelerr():
+    """Where the log-mel error sits: worst element of the fused reference-normalised output, the mel power error at
+    that element, and the error of the float32 oracle (numpy / scipy in float32) against the float64 one beside it."""
+    from yoho_b200 import preprocessing as pp
+    x = synth_batch(3, 480000)
+    want = fe.log_mel(x, norm_mode=1)
+    want32 = fe.log_mel(x, norm_mode=1, dtype=np.float32)
+    got = pp.log_mel_spectogram(x, norm="reference")
+    pw = fe.mel_spectogram(x.astype(np.float64), 400, 160, 16000, 80)
+    pg = pp.mel_spectogram(x, 400, 160, 16000, 80)
+    err = np.abs(got - want)
+    b, f, m = np.unravel_index(err.argmax(), err.shape)
+    print(f"[logmelerr] max abs err {err.max():.3e} at clip {b} frame {f} mel {m}: got {got[b, f, m]:.6f} want {want[b, f, m]:.6f}; "
+          f"float32 oracle err {np.abs(want32 - want).max():.3e}")
+    rel = np.abs(pg - pw) / np.maximum(pw, 1e-30)
+    print(f"[logmelerr] mel power there: got {pg[b, f, m]:.6e} want {pw[b, f, m]:.6e} rel {rel[b, f, m]:.3e}; frame max power {pw[b, f].max():.3e}")
+    big = pw > 1e-12
+    rb, rf, rm = np.unravel_index(np.where(big, rel, 0).argmax(), rel.shape)
+    print(f"[logmelerr] worst relative power error (power > 1e-12): {rel[rb, rf, rm]:.3e} at clip {rb} frame {rf} mel {rm} (power {pw[rb, rf, rm]:.3e}, frame max {pw[rb, rf].max():.3e})")
+    for q in (50, 90, 99, 99.9, 99.99):
+        print(f"[logmelerr]   percentile {q}: abs err {np.percentile(err, q):.3e}   rel power err {np.percentile(rel[big], q):.3e}")
+    frames = np.unique(np.argwhere(err > 5e-5)[:, 1])
+    print(f"[logmelerr] frames with an element above 5e-5: {frames[:40].tolist()} ({len(frames)} frames)")
 
 
 def stage_decperf():

@@ -134,30 +134,9 @@ extern "C" int yoho_ctx_create(int device, yoho_ctx** out) {
   ctx->cc_major = prop.major;
   ctx->cc_minor = prop.minor;
 
-  // Periodic Hann, scipy.signal.get_window('hann', 400): float64 then rounded to float32, exactly
-  // what jax.scipy.signal.stft multiplies by (reference audio.py:33).
-  const double kPi = 3.14159265358979323846;
-  std::vector<float> win(400);
-  double wsum = 0.0;
-  for (int n = 0; n < 400; ++n) {
-    win[n] = float(0.5 - 0.5 * std::cos(2.0 * kPi * n / 400.0));
-    wsum += double(win[n]);
-  }
-  ctx->window_sum = wsum;
-  std::vector<float2> tw(400);
-  for (int k1 = 0; k1 < 20; ++k1)
-    for (int n2 = 0; n2 < 20; ++n2) {
-      double ang = -2.0 * kPi * double(n2 * k1) / 400.0;
-      tw[k1 * 20 + n2] = make_float2(float(std::cos(ang)), float(std::sin(ang)));
-    }
+  // Periodic Hann window and twiddles of the 400-point transform go to the frontend's constant tables.
+  if (int rc = frontend_upload_constants(&ctx->window_sum)) { delete ctx; return rc; }
   cudaError_t e;
-  if ((e = cudaMalloc(&ctx->d_window, 400 * sizeof(float))) != cudaSuccess ||
-      (e = cudaMalloc(&ctx->d_twiddle, 400 * sizeof(float2))) != cudaSuccess ||
-      (e = cudaMemcpy(ctx->d_window, win.data(), 400 * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess ||
-      (e = cudaMemcpy(ctx->d_twiddle, tw.data(), 400 * sizeof(float2), cudaMemcpyHostToDevice)) != cudaSuccess) {
-    yoho_ctx_destroy(ctx);
-    return fail(YOHO_ERR_CUDA, "yoho_ctx_create: %s", cudaGetErrorString(e));
-  }
   // cuTensorMapEncodeTiled without linking libcuda.
   cudaDriverEntryPointQueryResult qres;
   void* fn = nullptr;
@@ -173,8 +152,6 @@ extern "C" int yoho_ctx_create(int device, yoho_ctx** out) {
 
 extern "C" int yoho_ctx_destroy(yoho_ctx* ctx) {
   if (!ctx) return YOHO_OK;
-  if (ctx->d_window) cudaFree(ctx->d_window);
-  if (ctx->d_twiddle) cudaFree(ctx->d_twiddle);
   delete ctx;
   return YOHO_OK;
 }
@@ -186,8 +163,8 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
   if (n_mels <= 0 || n_bins <= 0) return fail(YOHO_ERR_INVALID, "yoho_filterbank_create: shape (%d, %d)", n_mels, n_bins);
   DeviceGuard guard(ctx->device);
   if (guard.error != cudaSuccess) return fail(YOHO_ERR_CUDA, "yoho_filterbank_create: cudaSetDevice(%d): %s", ctx->device, cudaGetErrorString(guard.error));
-  if (n_mels > kMelWarps * kMelMaxRounds) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: n_mels=%d > %d", n_mels, kMelWarps * kMelMaxRounds);
-  if (n_bins > kMelPRows) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: n_bins=%d > %d", n_bins, kMelPRows);
+  if (n_mels > kMelMaxBands) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: n_mels=%d > %d", n_mels, kMelMaxBands);
+  if (n_bins > kMelBins) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: n_bins=%d > %d", n_bins, kMelBins);
   std::vector<int> lo(n_mels, 0), len(n_mels, 0);
   for (int m = 0; m < n_mels; ++m) {
     int first = -1, last = -1;
@@ -198,40 +175,43 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
   std::vector<int> order(n_mels);
   for (int m = 0; m < n_mels; ++m) order[m] = m;
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return len[a] > len[b]; });
-  MelSchedule sched = {};
-  sched.rounds = (n_mels + kMelWarps - 1) / kMelWarps;
-  for (int r = 0; r < sched.rounds; ++r) {
-    int n4 = (len[order[r * kMelWarps]] + 3) / 4;      // the round's longest band comes first
-    if (n4 > 255) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: band of %d bins", len[order[r * kMelWarps]]);
-    sched.n4[r] = (unsigned char)n4;
-  }
-  const int stride = 4 * (sched.n4[0] > 0 ? sched.n4[0] : 1);
-  if (size_t(n_mels) * stride > size_t(kMelMaxWeights))
-    return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: %d bands x %d bins exceed the kernel's %d-float weight tile", n_mels, stride, kMelMaxWeights);
   // |2 X[k]|^2 comes out of the packed-pair FFT; stft scales by 1/sum(w) (scaling='spectrum').
   const double scale = 0.25 / (ctx->window_sum * ctx->window_sum);
-  std::vector<float> w(size_t(n_mels) * stride, 0.0f);
-  std::vector<int2> bands(n_mels);
-  for (int r = 0; r < n_mels; ++r) {
-    const int m = order[r], walked = 4 * sched.n4[r / kMelWarps];
-    const int first = lo[m] + walked <= kMelPRows ? lo[m] : kMelPRows - walked;   // keep the walk inside the power tile
-    bands[r] = make_int2(m, first);
-    for (int j = 0; j < len[m]; ++j)
-      w[size_t(r) * stride + (lo[m] - first) + j] = float(double(host_filters[size_t(m) * n_bins + lo[m] + j]) * scale);
+  const int n_pairs = (n_mels + 1) / 2;
+  std::vector<int4> bands(size_t(2) * n_pairs);
+  std::vector<float2> w;
+  for (int p = 0; p < n_pairs; ++p) {
+    const int trip = (len[order[2 * p]] + 1) & ~1;                 // the pair's longer band comes first; walked two bins a step
+    if (trip > n_bins - (n_bins & 1)) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: band of %d bins", len[order[2 * p]]);
+    for (int h = 0; h < 2; ++h) {
+      const int r = 2 * p + h;
+      if (r >= n_mels) { bands[r] = make_int4(-1, 0, int(w.size()) - trip, trip); continue; }   // odd n_mels: walks the partner's weights, stores nothing
+      const int m = order[r];
+      const int first = lo[m] + trip <= n_bins ? lo[m] : n_bins - trip;   // keep the walk inside the power tile
+      bands[r] = make_int4(m, first, int(w.size()), trip);
+      for (int j = 0; j < trip; ++j) {
+        const int k = first + j;
+        const float v = (k >= lo[m] && k < lo[m] + len[m]) ? float(double(host_filters[size_t(m) * n_bins + k]) * scale) : 0.0f;
+        w.push_back(make_float2(v, v));
+      }
+    }
   }
+  if (w.empty()) w.push_back(make_float2(0.0f, 0.0f));
+  if (w.size() > size_t(kMelMaxWeights))
+    return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: %zu walked bins exceed the kernel's %d-entry weight tile", w.size(), kMelMaxWeights);
   yoho_filterbank* fb = new (std::nothrow) yoho_filterbank();
   if (!fb) return fail(YOHO_ERR_INVALID, "yoho_filterbank_create: out of host memory");
   fb->device = ctx->device;
   fb->n_mels = n_mels;
   fb->n_bins = n_bins;
-  fb->band_stride = stride;
-  fb->sched = sched;
+  fb->n_pairs = n_pairs;
+  fb->n_weights = int(w.size());
   fb->power_scale = scale;
   cudaError_t e;
-  if ((e = cudaMalloc(&fb->d_bands, n_mels * sizeof(int2))) != cudaSuccess ||
-      (e = cudaMalloc(&fb->d_weights, w.size() * sizeof(float))) != cudaSuccess ||
-      (e = cudaMemcpy(fb->d_bands, bands.data(), n_mels * sizeof(int2), cudaMemcpyHostToDevice)) != cudaSuccess ||
-      (e = cudaMemcpy(fb->d_weights, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice)) != cudaSuccess) {
+  if ((e = cudaMalloc(&fb->d_bands, bands.size() * sizeof(int4))) != cudaSuccess ||
+      (e = cudaMalloc(&fb->d_weights, w.size() * sizeof(float2))) != cudaSuccess ||
+      (e = cudaMemcpy(fb->d_bands, bands.data(), bands.size() * sizeof(int4), cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(fb->d_weights, w.data(), w.size() * sizeof(float2), cudaMemcpyHostToDevice)) != cudaSuccess) {
     yoho_filterbank_destroy(fb);
     return fail(YOHO_ERR_CUDA, "yoho_filterbank_create: %s", cudaGetErrorString(e));
   }

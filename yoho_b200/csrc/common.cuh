@@ -65,26 +65,30 @@ struct yoho_ctx {
   int device = -1;
   int num_sms = 0;
   int cc_major = 0, cc_minor = 0;
-  // frontend constants for n_fft = 400 (built in double on the host, stored as float32)
-  float* d_window = nullptr;    // periodic Hann (400)
-  float2* d_twiddle = nullptr;  // W_400^(n2*k1) laid out [k1][n2] (20 x 20)
-  double window_sum = 0.0;      // sum of the float32-rounded window
+  // frontend constants for n_fft = 400 (built in double on the host, stored as float32 in the kernel's constant bank:
+  // frontend_upload_constants)
+  double window_sum = 0.0;      // sum of the float32-rounded periodic Hann window
   void* encode_tiled = nullptr; // cuTensorMapEncodeTiled driver entry point
 };
 
-// Mel filterbank as the log-mel kernel consumes it: bands sorted longest first and dealt to the kernel's
-// kMelWarps warps round by round (boustrophedon); every band of a round is walked 4 * round_n4 bins.
-constexpr int kMelWarps = 10;          // warps of logmel_kernel
-constexpr int kMelPRows = 204;         // rows of the kernel's power tile: 201 bins rounded up to the 4-bin step
-constexpr int kMelMaxRounds = 16;      // n_mels <= 160
-constexpr int kMelMaxWeights = 3072;   // floats of band weights held in shared memory
-struct MelSchedule { int rounds; unsigned char n4[kMelMaxRounds]; };
+namespace yoho {
+// Uploads the periodic Hann window and the W_400 twiddles into logmel_kernel's __constant__ tables on the current
+// device (called by yoho_ctx_create); returns the sum of the float32-rounded window through *window_sum.
+int frontend_upload_constants(double* window_sum);
+}
+
+// Mel filterbank as the log-mel kernel consumes it.  Every mel row is a band [first, first + trip) of FFT bins; bands are
+// sorted longest first and taken two at a time (one per half warp, lane = frame pair), so both bands of a pair are walked
+// `trip` bins (the longer one's length rounded up to even) with zero weights past their own end.
+constexpr int kMelMaxBands = 128;      // n_mels <= 128 (band pairs * 2)
+constexpr int kMelMaxWeights = 600;    // (w, w) entries held in shared memory: sum over bands of their pair's trip
+constexpr int kMelBins = 201;          // n_fft / 2 + 1
 struct yoho_filterbank {
   int device = -1;
   int n_mels = 0, n_bins = 0;
-  int band_stride = 0;        // floats per row in d_weights (multiple of 4)
-  MelSchedule sched = {};
-  int2* d_bands = nullptr;    // sorted position -> {mel row, first bin walked}
-  float* d_weights = nullptr; // (n_mels, band_stride) in sorted order, zero padded, already multiplied by the STFT power scale
+  int n_pairs = 0;            // band pairs, sorted by trip (descending)
+  int n_weights = 0;          // float2 entries in d_weights
+  int4* d_bands = nullptr;    // [2 * n_pairs] {mel row or -1, first bin walked, offset into d_weights, trip}
+  float2* d_weights = nullptr; // (w, w) per walked bin, already multiplied by the STFT power scale
   double power_scale = 0.0;   // 0.25 / window_sum^2 folded into d_weights
 };

@@ -11,99 +11,135 @@
 //   out   (B, F, M)     float32, time-major / mel-last (what audio.py:36's einsum returns)
 //   stats (B, tiles, 2) float32 per-tile partials {sum, sum of squares} or {max, -}
 //
-// One tile = 32 consecutive frames of one clip = 16 complex FFTs of length 400, two real frames
-// packed as (re, im).  400 = 20 x 20: each FFT is run by 20 threads, each doing one radix-20
-// butterfly per pass entirely in registers (radix-20 = 4 x 5 by the prime-factor map, so no
-// internal twiddles), with one shared-memory transpose between the passes.  The kernel is
-// persistent (two CTAs per SM walk the (clip, tile) list): the 5360 PCM samples of the NEXT tile
-// are fetched with 16-byte cp.async into the second half of a double buffer while the current tile
-// is transformed (each sample is used by 2.5 frames; int16 is converted when it is read).  The two
-// real spectra are untangled from Z[k], Z[400-k] through registers and the power spectrum is
-// written back over Z bin-major, P[k][frame].  The mel bands (<= 2 filters touch any FFT bin) are
-// then applied with lane = frame: a warp takes whole bands (dealt longest-first, boustrophedon,
-// so the ten warps get equal work), the band's weights are warp-uniform 128-bit loads, there is
-// no divergence, and the (32 frames x n_mels) result is transposed through shared memory so the
-// global stores are full 128-byte lines.
+// The kernel is bound by shared-memory bandwidth and instruction issue, not by HBM (2.9 MB and ~30 MFLOP per clip), so
+// its design minimises shared-memory wavefronts and issue slots per frame:
+//
+//   * One tile = 32 consecutive frames of one clip = 16 complex FFTs of length 400 (two real frames packed as re/im).
+//     400 = 20 x 20; a thread does radix-20 butterflies (prime-factor 4 x 5, no internal twiddles) in registers.
+//   * Every thread works on TWO columns at once in packed fp32 pairs (add/mul/fma.f32x2: one issue slot for two lanes
+//     of work), structure-of-arrays: a register pair holds the real (or imaginary) parts of the two columns, so complex
+//     arithmetic needs no swaps and the +-i rotations of the butterflies are free.
+//   * lane <-> FFT (8 FFTs x 2 column pairs per half warp), warp <-> column pair: window and twiddle factors are the same for
+//     all FFTs of a column pair and come from the constant bank, not from shared memory; every shared-memory access of the
+//     two passes is bank-conflict free by construction (padding of 16 bytes per 320 samples, 21-row blocks, XOR swizzle of P).
+//   * Pass 1 (columns 2t, 2t+1 of x[20 n1 + n2]): frame B = frame A shifted by 160 samples = 8 rows, so 28 row loads serve
+//     both frames.  Its outputs are written for pass 2 as the pair (column j, column 20-j): E_j = D_j T_j and
+//     conj(D_{20-j}) T_j with one twiddle T_j = W_400^(n2 j) for both.
+//   * Pass 2 transforms the pair (E_j, conj-reversed E_{20-j}) in one packed radix-20: slot x then holds Z[k] and slot y
+//     conj(Z[400-k]) at the SAME register index, so the two real spectra are untangled and squared in registers
+//     (|2 X_A[k]|^2, |2 X_B[k]|^2 = U^2 + V^2 with U, V sums / differences of the halves): no Z round trip through shared
+//     memory.  Columns 0 and 10 are their own partners and take a scalar variant in one half warp.
+//   * Power goes to shared memory bin-major over the (dead) PCM tile; the mel bands (<= 2 filters touch any FFT bin) are
+//     applied with lane = frame PAIR (packed FMA) and two bands per warp, longest first; the (32 frames x n_mels) result is
+//     transposed through shared memory so the global stores are full 128-byte lines.
+//   * Persistent CTAs (two per SM) walk the (clip, tile) list; the PCM of the next tile arrives by 16-byte zero-filling
+//     cp.async into the other slot while the current tile is transformed (int16 is converted when it is read).
 #include "common.cuh"
+#include "ptx_sm100.cuh"
+
+#include <cmath>
+#include <cstdlib>
+#include <vector>
 
 namespace yoho {
 
+using ptx::add_f32x2;
+using ptx::fma_f32x2;
+using ptx::mul_f32x2;
+using ptx::pack_f32x2;
+using ptx::unpack_f32x2;
+
 constexpr int kNfft = 400;
 constexpr int kHop = 160;
-constexpr int kBins = 201;
+constexpr int kBins = kMelBins;                                   // 201
 constexpr int kFramesPerCta = 32;
-constexpr int kFftsPerCta = kFramesPerCta / 2;
-constexpr int kThreads = kFftsPerCta * 20;                      // 320
+constexpr int kFftsPerCta = kFramesPerCta / 2;                    // 16
+constexpr int kThreads = 160;                                     // 10 column-pair tasks x 16 FFTs
+constexpr int kWarps = kThreads / 32;                             // 5
 constexpr int kTileSamples = (kFramesPerCta - 1) * kHop + kNfft;  // 5360
-constexpr int kERow = 21;                                       // padded row (float2) of the transpose buffer
-constexpr int kEFft = 20 * kERow;                               // 420 float2 per FFT
-constexpr int kZFft = 404;                                      // float2 per FFT of Z: 808 words = 8 mod 32 keeps the 20-thread groups off each other's banks
-constexpr int kPRow = kFramesPerCta + 1;                        // floats per bin row of P[k][frame]: odd, so bin-strided writes spread over the banks
-constexpr int kPRows = kMelPRows;                               // 201 bins, rounded up: bands are walked four bins at a time
-constexpr int kMaxMels = kMelWarps * kMelMaxRounds;             // the output transpose buffer holds 32 x (n_mels | 1) floats
-constexpr int kWarps = kThreads / 32;
-static_assert(kWarps == kMelWarps, "the filterbank's round schedule is built for this many warps");
+constexpr int kEBlockRows = 21;                                   // rows per k1 block of E: 20 + 1 so that neighbouring blocks differ in row parity
+constexpr int kERows = 20 * kEBlockRows;                          // 420 rows of 16 floats (one per FFT)
+constexpr int kPRow = kFramesPerCta;                              // floats per bin row of P[k][frame]
+constexpr int kPBytes = kBins * kPRow * 4;                        // 25 728
+
+// window[t][n1] = (w[20 n1 + 2t], w[20 n1 + 2t + 1]); [0] plain, [1] times 1/32768 (int16 PCM, whisper.py:249)
+__constant__ float2 c_win[2][10][20];
+// twiddle[t][j] = (Re T lo, Re T hi, Im T lo, Im T hi), T = W_400^(n2 j) for n2 = 2t (lo) and 2t + 1 (hi), j = 1..10
+__constant__ float4 c_tw[10][11];
 
 template <typename T>
 struct FrontendSmem {
-  T raw[2][kTileSamples];          // double-buffered PCM tile, as it lies in global memory
-  float2 ez[kFftsPerCta * kEFft];  // pass-1 -> pass-2 transpose; then Z in natural order; then the power spectrum
-  float mel_w[kMelMaxWeights];     // band weights, sorted order (resident for the whole kernel)
-  int2 mel_band[kMaxMels];
+  static constexpr int kPad = 16 / int(sizeof(T));                // elements of padding after every 320 samples
+  static constexpr int kFftStride = 320 + kPad;                   // elements between the first samples of consecutive FFTs
+  static constexpr int kRawElems = kTileSamples + 17 * kPad;
+  static constexpr int kSlotBytes = kPBytes > int(kRawElems * sizeof(T)) ? kPBytes : int(kRawElems * sizeof(T));
+  // slot[b]: PCM of the tile being staged / transformed; after pass 1 the samples are dead and the slot takes the tile's
+  // power spectrum P[bin][frame]
+  alignas(16) unsigned char slot[2][kSlotBytes];
+  // pass-1 -> pass-2 transpose, structure of arrays: e_re / e_im [k1 block][position of n2][fft]; after pass 2 has
+  // loaded it, the (32 frames x n_mels|1) output tile
+  alignas(16) float e_re[kERows * kFftsPerCta];
+  float e_im[kERows * kFftsPerCta];
+  alignas(16) float4 tw[10][11];              // copies of c_tw / c_win[this T]: read with two addresses per warp (one per task),
+  float2 win[10][20];                         // which shared memory broadcasts in one wavefront and the constant cache serialises
+  alignas(16) float2 mel_w[kMelMaxWeights];   // (w, w) per walked bin (resident for the whole kernel)
+  int4 mel_band[kMelMaxBands];
   float red[2 * 32];
 };
-static_assert(kFftsPerCta * kZFft <= kFftsPerCta * kEFft, "Z must fit in the transpose buffer");
-static_assert(kPRows * kPRow + kFramesPerCta * (kMaxMels | 1) <= 2 * kFftsPerCta * kEFft, "P and the output tile overlay the transpose buffer");
-static_assert((kTileSamples * sizeof(int16_t)) % 16 == 0, "second PCM buffer stays 16-byte aligned");
+static_assert(kFramesPerCta * kMelMaxBands * 4 <= kERows * kFftsPerCta * 4, "the output tile overlays e_re");
 
-// ---- radix-20 butterfly (prime-factor 4 x 5), forward sign ------------------------------
-__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
-__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
-  return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+// ---- two complex numbers in packed fp32 pairs (structure of arrays) -------------------------------------------------
+struct C2 { uint64_t re, im; };
+__device__ __forceinline__ uint64_t sub_f32x2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
 }
-// multiply by -i
-__device__ __forceinline__ float2 mul_mi(float2 a) { return make_float2(a.y, -a.x); }
+__device__ __forceinline__ C2 cadd(C2 a, C2 b) { return {add_f32x2(a.re, b.re), add_f32x2(a.im, b.im)}; }
+__device__ __forceinline__ C2 csub(C2 a, C2 b) { return {sub_f32x2(a.re, b.re), sub_f32x2(a.im, b.im)}; }
+// a - i b and a + i b (the rotations cost nothing in this layout: they only exchange the roles of re and im)
+__device__ __forceinline__ C2 sub_i(C2 a, C2 b) { return {add_f32x2(a.re, b.im), sub_f32x2(a.im, b.re)}; }
+__device__ __forceinline__ C2 add_i(C2 a, C2 b) { return {sub_f32x2(a.re, b.im), add_f32x2(a.im, b.re)}; }
+__device__ __forceinline__ uint64_t dup(float c) { return pack_f32x2(c, c); }
 
-__device__ __forceinline__ void dft4(float2 a, float2 b, float2 c, float2 d, float2& o0, float2& o1,
-                                     float2& o2, float2& o3) {
-  float2 s02 = cadd(a, c), d02 = csub(a, c), s13 = cadd(b, d), d13 = mul_mi(csub(b, d));
+__device__ __forceinline__ void dft4(C2 a, C2 b, C2 c, C2 d, C2& o0, C2& o1, C2& o2, C2& o3) {
+  const C2 s02 = cadd(a, c), d02 = csub(a, c), s13 = cadd(b, d), e = csub(b, d);
   o0 = cadd(s02, s13);
   o2 = csub(s02, s13);
-  o1 = cadd(d02, d13);
-  o3 = csub(d02, d13);
+  o1 = sub_i(d02, e);    // d02 - i (b - d)
+  o3 = add_i(d02, e);
 }
 
-__device__ __forceinline__ void dft5(float2 x0, float2 x1, float2 x2, float2 x3, float2 x4, float2& o0,
-                                     float2& o1, float2& o2, float2& o3, float2& o4) {
-  constexpr float c1 = 0.30901699437494742f;   // cos(2 pi / 5)
-  constexpr float c2 = -0.80901699437494742f;  // cos(4 pi / 5)
-  constexpr float s1 = 0.95105651629515357f;   // sin(2 pi / 5)
-  constexpr float s2 = 0.58778525229247313f;   // sin(4 pi / 5)
-  float2 p1 = cadd(x1, x4), m1 = csub(x1, x4), p2 = cadd(x2, x3), m2 = csub(x2, x3);
-  o0 = make_float2(x0.x + p1.x + p2.x, x0.y + p1.y + p2.y);
-  float2 a1 = make_float2(fmaf(c2, p2.x, fmaf(c1, p1.x, x0.x)), fmaf(c2, p2.y, fmaf(c1, p1.y, x0.y)));
-  float2 a2 = make_float2(fmaf(c1, p2.x, fmaf(c2, p1.x, x0.x)), fmaf(c1, p2.y, fmaf(c2, p1.y, x0.y)));
-  float2 b1 = make_float2(fmaf(s2, m2.x, s1 * m1.x), fmaf(s2, m2.y, s1 * m1.y));
-  float2 b2 = make_float2(fmaf(-s1, m2.x, s2 * m1.x), fmaf(-s1, m2.y, s2 * m1.y));
+__device__ __forceinline__ void dft5(C2 x0, C2 x1, C2 x2, C2 x3, C2 x4, C2& o0, C2& o1, C2& o2, C2& o3, C2& o4) {
+  const uint64_t c1 = dup(0.30901699437494742f);    // cos(2 pi / 5)
+  const uint64_t c2 = dup(-0.80901699437494742f);   // cos(4 pi / 5)
+  const uint64_t s1 = dup(0.95105651629515357f);    // sin(2 pi / 5)
+  const uint64_t s2 = dup(0.58778525229247313f);    // sin(4 pi / 5)
+  const uint64_t ns1 = dup(-0.95105651629515357f);
+  const C2 p1 = cadd(x1, x4), m1 = csub(x1, x4), p2 = cadd(x2, x3), m2 = csub(x2, x3);
+  o0 = cadd(x0, cadd(p1, p2));
+  const C2 a1 = {fma_f32x2(c2, p2.re, fma_f32x2(c1, p1.re, x0.re)), fma_f32x2(c2, p2.im, fma_f32x2(c1, p1.im, x0.im))};
+  const C2 a2 = {fma_f32x2(c1, p2.re, fma_f32x2(c2, p1.re, x0.re)), fma_f32x2(c1, p2.im, fma_f32x2(c2, p1.im, x0.im))};
+  const C2 b1 = {fma_f32x2(s2, m2.re, mul_f32x2(s1, m1.re)), fma_f32x2(s2, m2.im, mul_f32x2(s1, m1.im))};
+  const C2 b2 = {fma_f32x2(ns1, m2.re, mul_f32x2(s2, m1.re)), fma_f32x2(ns1, m2.im, mul_f32x2(s2, m1.im))};
   // X1 = a1 - i b1, X4 = a1 + i b1, X2 = a2 - i b2, X3 = a2 + i b2
-  o1 = make_float2(a1.x + b1.y, a1.y - b1.x);
-  o4 = make_float2(a1.x - b1.y, a1.y + b1.x);
-  o2 = make_float2(a2.x + b2.y, a2.y - b2.x);
-  o3 = make_float2(a2.x - b2.y, a2.y + b2.x);
+  o1 = sub_i(a1, b1);
+  o4 = add_i(a1, b1);
+  o2 = sub_i(a2, b2);
+  o3 = add_i(a2, b2);
 }
 
-// v[n] -> v[k], 20-point forward DFT.  n = (5 n1 + 4 n2) mod 20, k = (5 k1 + 16 k2) mod 20.
-__device__ __forceinline__ void dft20(float2 (&v)[20]) {
-  float2 t[4][5];
+// v[n] -> v[k], 20-point forward DFT of both packed columns.  n = (5 n1 + 4 n2) mod 20, k = (5 k1 + 16 k2) mod 20.
+__device__ __forceinline__ void dft20(C2 (&v)[20]) {
+  C2 t[4][5];
 #pragma unroll
   for (int n2 = 0; n2 < 5; ++n2)
-    dft4(v[(4 * n2) % 20], v[(5 + 4 * n2) % 20], v[(10 + 4 * n2) % 20], v[(15 + 4 * n2) % 20], t[0][n2],
-         t[1][n2], t[2][n2], t[3][n2]);
+    dft4(v[(4 * n2) % 20], v[(5 + 4 * n2) % 20], v[(10 + 4 * n2) % 20], v[(15 + 4 * n2) % 20], t[0][n2], t[1][n2], t[2][n2],
+         t[3][n2]);
 #pragma unroll
   for (int k1 = 0; k1 < 4; ++k1)
-    dft5(t[k1][0], t[k1][1], t[k1][2], t[k1][3], t[k1][4], v[(5 * k1) % 20], v[(5 * k1 + 16) % 20],
-         v[(5 * k1 + 32) % 20], v[(5 * k1 + 48) % 20], v[(5 * k1 + 64) % 20]);
+    dft5(t[k1][0], t[k1][1], t[k1][2], t[k1][3], t[k1][4], v[(5 * k1) % 20], v[(5 * k1 + 16) % 20], v[(5 * k1 + 32) % 20],
+         v[(5 * k1 + 48) % 20], v[(5 * k1 + 64) % 20]);
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -123,9 +159,24 @@ __device__ __forceinline__ float lg2_approx(float x) {
   return y;
 }
 
-template <typename T> __device__ __forceinline__ float pcm_to_float(T v);
-template <> __device__ __forceinline__ float pcm_to_float<float>(float v) { return v; }
-template <> __device__ __forceinline__ float pcm_to_float<int16_t>(int16_t v) { return float(v) * (1.0f / 32768.0f); }
+// two consecutive samples as a packed float pair
+template <typename T> __device__ __forceinline__ uint64_t load_pair(const T* p);
+template <> __device__ __forceinline__ uint64_t load_pair<float>(const float* p) { return *reinterpret_cast<const uint64_t*>(p); }
+template <> __device__ __forceinline__ uint64_t load_pair<int16_t>(const int16_t* p) {
+  const uint32_t w = *reinterpret_cast<const uint32_t*>(p);
+  return pack_f32x2(float(int(short(w & 0xffffu))), float(int(w) >> 16));     // the 1/32768 lives in the window table
+}
+
+__device__ __forceinline__ uint64_t lds_u64(uint32_t addr) {
+  uint64_t v;
+  asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
 
 __device__ __forceinline__ void cp_async_16_zfill(void* smem_dst, const void* gmem_src, int src_bytes) {
   uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
@@ -134,186 +185,293 @@ __device__ __forceinline__ void cp_async_16_zfill(void* smem_dst, const void* gm
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// Start copying samples [s0, s0 + kTileSamples) of one clip into shared memory, zero past `valid`
-// (the stft tail padding, audio.py:33 `padded=True`, and the short last clip of a long recording).
+// Start copying samples [s0, s0 + kTileSamples) of one clip into a slot, zero past `valid` (the stft tail padding,
+// audio.py:33 `padded=True`, and the short last clip of a long recording).  Sample n of the tile lands at element
+// n + kPad * (n / 320): 16 bytes of padding after every 320 samples put consecutive FFTs 8 (float) / 4 (int16) banks apart.
 // vec_ok: clip base and length are 16-byte multiples, so every chunk is one zero-filling cp.async.
 template <typename T>
-__device__ __forceinline__ void stage_pcm_async(T* dst, const T* __restrict__ pcm, size_t clip_off, int s0, int valid,
-                                                bool vec_ok) {
-  constexpr int kVec = 16 / sizeof(T);  // elements per 128-bit chunk
+__device__ __forceinline__ void stage_pcm_async(T* dst, const T* __restrict__ pcm, size_t clip_off, int s0, int valid, bool vec_ok) {
+  constexpr int kVec = 16 / sizeof(T);          // elements per 128-bit chunk
+  constexpr int kChunks = kTileSamples / kVec;  // 1340 / 670
+  constexpr int kChunksPerBlock = 320 / kVec;   // a chunk never straddles a 320-sample block
+  static_assert(kTileSamples % kVec == 0 && 320 % kVec == 0, "chunking");
   const T* clip = pcm + clip_off;
-  if (vec_ok && s0 + kTileSamples <= valid) {      // interior tile: every chunk is whole
-    const T* src = clip + s0;
+  static_assert(kThreads % kChunksPerBlock == 0, "a thread's chunks advance by whole 320-sample blocks");
+  if (vec_ok && s0 + kTileSamples <= valid) {
+    // interior tile: chunk c = tid + it * kThreads lands at c * kVec + kVec * (c / kChunksPerBlock); both advance by constants
+    T* d = dst + threadIdx.x * kVec + kVec * (threadIdx.x / kChunksPerBlock);
+    const T* s = clip + s0 + threadIdx.x * kVec;
+    constexpr int kFull = kChunks / kThreads, kRem = kChunks % kThreads;
 #pragma unroll
-    for (int i = threadIdx.x * kVec, it = 0; it < (kTileSamples + kThreads * kVec - 1) / (kThreads * kVec); ++it, i += kThreads * kVec)
-      if (i < kTileSamples) cp_async_16_zfill(dst + i, src + i, 16);
+    for (int it = 0; it < kFull; ++it)
+      cp_async_16_zfill(d + it * (kThreads + kThreads / kChunksPerBlock) * kVec, s + it * kThreads * kVec, 16);
+    if (kRem && int(threadIdx.x) < kRem)
+      cp_async_16_zfill(d + kFull * (kThreads + kThreads / kChunksPerBlock) * kVec, s + kFull * kThreads * kVec, 16);
   } else if (vec_ok) {
-    for (int i = threadIdx.x * kVec; i < kTileSamples; i += kThreads * kVec) {
-      int g = s0 + i;
-      int n = valid - g;
-      n = n < 0 ? 0 : (n > kVec ? kVec : n);
-      cp_async_16_zfill(dst + i, n > 0 ? clip + g : pcm, n * int(sizeof(T)));
+#pragma unroll 1
+    for (int c = threadIdx.x; c < kChunks; c += kThreads) {
+      const int n = c * kVec, g = s0 + n;
+      int left = valid - g;
+      left = left < 0 ? 0 : (left > kVec ? kVec : left);
+      cp_async_16_zfill(dst + n + kVec * (c / kChunksPerBlock), left > 0 ? clip + g : pcm, left * int(sizeof(T)));
     }
   } else {
-    for (int i = threadIdx.x; i < kTileSamples; i += kThreads) {
-      int g = s0 + i;
-      dst[i] = g < valid ? __ldg(clip + g) : T(0);
+    for (int n = threadIdx.x; n < kTileSamples; n += kThreads) {
+      const int g = s0 + n;
+      dst[n + kVec * (n / 320)] = g < valid ? __ldg(clip + g) : T(0);
     }
   }
 }
 
-// norm: 0 mel power, 1 log10(max(x,1e-13)) + {sum,sumsq} partials, 2 log10(max(x,1e-10)) + {max} partials
+// E[block][pos][fft]: the element of column n2 sits at row block * 21 + pos(n2), pos = n2 / 2 + 10 * (n2 & 1)
+__device__ __forceinline__ int e_index(int block, int pos, int fft) { return (block * kEBlockRows + pos) * kFftsPerCta + fft; }
+
+// Two bands' worth (one per half warp) of kSteps x 2 bins for one frame pair: sum_i P[first + i][frames] * w_i.  a0 / a1
+// address the even / odd steps' rows (odd bins keep their 16-frame halves exchanged), wa the (w, w) table.
+template <int kSteps>
+__device__ __forceinline__ uint64_t mel_pair(uint32_t a0, uint32_t a1, uint32_t wa) {
+  uint64_t p0[kSteps], p1[kSteps];
+  float4 w[kSteps];
+#pragma unroll
+  for (int i = 0; i < kSteps; ++i) {
+    p0[i] = lds_u64(a0 + uint32_t(i) * (2 * kPRow * 4));
+    p1[i] = lds_u64(a1 + uint32_t(i) * (2 * kPRow * 4));
+    w[i] = lds_f4(wa + uint32_t(i) * 16u);                    // (w_2i, w_2i, w_2i+1, w_2i+1)
+  }
+  uint64_t s0 = mul_f32x2(p0[0], pack_f32x2(w[0].x, w[0].y)), s1 = mul_f32x2(p1[0], pack_f32x2(w[0].z, w[0].w));
+#pragma unroll
+  for (int i = 1; i < kSteps; ++i) {
+    s0 = fma_f32x2(p0[i], pack_f32x2(w[i].x, w[i].y), s0);
+    s1 = fma_f32x2(p1[i], pack_f32x2(w[i].z, w[i].w), s1);
+  }
+  return add_f32x2(s0, s1);
+}
+
+// |2 X_A[k]|^2 and |2 X_B[k]|^2 from a = Z[k], b = Z[400 - k] (frames A, B packed as re / im of one complex FFT)
+__device__ __forceinline__ float2 untangle_power(float ax, float ay, float bx, float by) {
+  const float ar = ax + bx, ai = ay - by, br = ay + by, bi = ax - bx;
+  return make_float2(fmaf(ar, ar, ai * ai), fmaf(br, br, bi * bi));
+}
+
+// kNorm: 0 mel power, 1 log10(max(x,1e-13)) + {sum,sumsq} partials, 2 log10(max(x,1e-10)) + {max} partials
 // Work item = clip0 * tiles_per_clip + i, i < n_items: clip = item / tiles_per_clip, tile = item % tiles_per_clip.
-template <typename T>
+template <typename T, int kNorm>
 __global__ void __launch_bounds__(kThreads, 2)
 logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples, int n_frames, int clip0, int n_items,
-              const float* __restrict__ window, const float2* __restrict__ twiddle,
-              const int2* __restrict__ fb_bands, const float* __restrict__ fb_w, int band_stride, int n_mels,
-              const __grid_constant__ MelSchedule sched, float* __restrict__ out,
-              float2* __restrict__ stats, int tiles_per_clip, int norm, int vec_ok) {
+              const int4* __restrict__ fb_bands, const float2* __restrict__ fb_w, int n_pairs, int n_weights, int n_mels,
+              float* __restrict__ out, float2* __restrict__ stats, int tiles_per_clip, int vec_ok, int vec_out) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  FrontendSmem<T>& sm = *reinterpret_cast<FrontendSmem<T>*>(smem_raw);
+  using Smem = FrontendSmem<T>;
+  Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
 
   const int tid = threadIdx.x;
-  const int fft = tid / 20;   // which pair of frames
-  const int lane20 = tid % 20;
   const int warp = tid >> 5, lane = tid & 31;
-  const float log_floor = (norm == YOHO_NORM_WHISPER) ? 1e-10f : 1e-13f;
-  const int o_stride = n_mels | 1;
+  // FFT roles: half warp hw holds FFTs 8 hw .. 8 hw + 7, each twice: sub = 0 / 1 are the warp's two column-pair tasks
+  const int fft = (lane & 7) + 8 * (lane >> 4);
+  const int task = 2 * warp + ((lane >> 3) & 1);          // pass 1: columns 2 task, 2 task + 1; pass 2: columns task, 20 - task
+  // mel roles: half warp h takes band h of the warp's current band pair, lane = frame pair
+  const int fp = lane & 15, mh = lane >> 4;
+  const float log_floor = (kNorm == YOHO_NORM_WHISPER) ? 1e-10f : 1e-13f;
+  constexpr int kWin = sizeof(T) == 2 ? 1 : 0;
 
   auto stage = [&](int item, int buf) {
     int clip = clip0 + item / tiles_per_clip, tile = item % tiles_per_clip;
     // samples of this clip that exist in `pcm` (a long recording's last clip is short: zero padded, whisper.py:253)
     const long long left = total_samples - (long long)clip * n_samples;
     const int valid = left >= n_samples ? n_samples : (left > 0 ? int(left) : 0);
-    stage_pcm_async<T>(sm.raw[buf], pcm, size_t(clip) * n_samples, tile * kFramesPerCta * kHop, valid, vec_ok != 0);
+    stage_pcm_async<T>(reinterpret_cast<T*>(sm.slot[buf]), pcm, size_t(clip) * n_samples, tile * kFramesPerCta * kHop, valid, vec_ok != 0);
   };
 
   int item = blockIdx.x;
   if (item >= n_items) return;
-  float win[20];
-#pragma unroll
-  for (int n1 = 0; n1 < 20; ++n1) win[n1] = __ldg(window + 20 * n1 + lane20);
   stage(item, 0);
   cp_async_commit();
-  for (int i = tid; i < n_mels * band_stride; i += kThreads) sm.mel_w[i] = __ldg(fb_w + i);
-  for (int i = tid; i < n_mels; i += kThreads) sm.mel_band[i] = __ldg(fb_bands + i);
+  for (int i = tid; i < 10 * 11; i += kThreads) (&sm.tw[0][0])[i] = (&c_tw[0][0])[i];
+  for (int i = tid; i < 10 * 20; i += kThreads) (&sm.win[0][0])[i] = (&c_win[kWin][0][0])[i];
+  for (int i = tid; i < n_weights; i += kThreads) sm.mel_w[i] = __ldg(fb_w + i);
+  for (int i = tid; i < 2 * n_pairs; i += kThreads) sm.mel_band[i] = __ldg(fb_bands + i);
 
   for (int buf = 0; item < n_items; item += gridDim.x, buf ^= 1) {
     const int clip = clip0 + item / tiles_per_clip, tile = item % tiles_per_clip;
     cp_async_wait_all();
-    __syncthreads();  // this tile's samples have landed; the previous tile's power rows and red[] are free
+    __syncthreads();  // this tile's samples have landed; the previous tile's power rows (other slot), output tile and red[] are free
     if (item + int(gridDim.x) < n_items) stage(item + gridDim.x, buf ^ 1);
     cp_async_commit();
 
-    float2 v[20];
-    // ---- pass 1: this thread owns n2 = lane20; DFT over n1 of x[20 n1 + n2] -----------------
+    C2 v[20];
+    // ---- pass 1: columns n2 = 2 task, 2 task + 1; DFT over n1 of x[20 n1 + n2], frames A / B as re / im ------------------
     {
-      const T* fa = sm.raw[buf] + (2 * fft) * kHop + lane20;  // frame A -> real part
-      const T* fb = fa + kHop;                                // frame B -> imaginary part
+      const T* src = reinterpret_cast<const T*>(sm.slot[buf]) + fft * Smem::kFftStride + 2 * task;
+      uint64_t r[28];          // rows 0..19 are frame A; frame B starts 160 samples = 8 rows later
 #pragma unroll
-      for (int n1 = 0; n1 < 20; ++n1)
-        v[n1] = make_float2(pcm_to_float<T>(fa[20 * n1]) * win[n1], pcm_to_float<T>(fb[20 * n1]) * win[n1]);
-      dft20(v);
-      float2* e = sm.ez + fft * kEFft + lane20;  // E[fft][k1][n2]
+      for (int i = 0; i < 28; ++i) r[i] = load_pair<T>(src + 20 * i + (i >= 16 ? Smem::kPad : 0));
 #pragma unroll
-      for (int k1 = 0; k1 < 20; ++k1) {
-        float2 tw = __ldg(twiddle + k1 * 20 + lane20);  // W_400^(n2 k1)
-        e[k1 * kERow] = cmul(v[k1], tw);
+      for (int n1 = 0; n1 < 20; ++n1) {
+        const float2 wf = sm.win[task][n1];
+        const uint64_t w = pack_f32x2(wf.x, wf.y);
+        v[n1].re = mul_f32x2(r[n1], w);
+        v[n1].im = mul_f32x2(r[n1 + 8], w);
       }
-    }
-    __syncthreads();
-    // ---- pass 2: this thread owns k1 = lane20; DFT over n2 -> Z[k1 + 20 k2] ------------------
-    {
-      const float2* e = sm.ez + fft * kEFft + lane20 * kERow;
+      dft20(v);              // v[k1] = D[k1][n2]
+      auto store = [&](int block, C2 val) {
+        float lo, hi;
+        unpack_f32x2(val.re, lo, hi);
+        sm.e_re[e_index(block, task, fft)] = lo;
+        sm.e_re[e_index(block, task + 10, fft)] = hi;
+        unpack_f32x2(val.im, lo, hi);
+        sm.e_im[e_index(block, task, fft)] = lo;
+        sm.e_im[e_index(block, task + 10, fft)] = hi;
+      };
+      store(0, v[0]);
 #pragma unroll
-      for (int n2 = 0; n2 < 20; ++n2) v[n2] = e[n2];
-      dft20(v);
-    }
-    __syncthreads();  // every thread has read its row before Z overwrites the buffer
-    {
-      float2* z = sm.ez + fft * kZFft + lane20;
-#pragma unroll
-      for (int k2 = 0; k2 < 20; ++k2) z[20 * k2] = v[k2];
-    }
-    __syncthreads();
-    // ---- untangle the two real spectra and take |.|^2 (scale folded into the mel weights) ----
-    // bins k = lane20 + 20 j of this thread's own FFT, through registers: the power rows of frames
-    // 2 fft and 2 fft + 1 replace Z of the same FFT.
-    {
-      const float2* z = sm.ez + fft * kZFft;
-      float pa[11], pb[11];
-#pragma unroll
-      for (int j = 0; j < 11; ++j) {
-        int k = lane20 + 20 * j;
-        if (j < 10 || lane20 == 0) {
-          float2 a = z[k];
-          float2 b = z[k == 0 ? 0 : 400 - k];
-          float ar = a.x + b.x, ai = a.y - b.y;  // 2 * X_A[k]
-          float br = a.y + b.y, bi = a.x - b.x;  // 2 * X_B[k] (up to a unit factor)
-          pa[j] = fmaf(ar, ar, ai * ai);
-          pb[j] = fmaf(br, br, bi * bi);
+      for (int j = 1; j <= 10; ++j) {
+        const float4 tw = sm.tw[task][j];                     // T = W_400^(n2 j)
+        const uint64_t tr = pack_f32x2(tw.x, tw.y), ti = pack_f32x2(tw.z, tw.w);
+        const C2 d = v[j];
+        // E_j = D_j T
+        store(j, {sub_f32x2(mul_f32x2(d.re, tr), mul_f32x2(d.im, ti)), fma_f32x2(d.re, ti, mul_f32x2(d.im, tr))});
+        if (j < 10) {
+          // partner column: conj(D_{20-j}) T  (pass 2 then finds conj(Z[400 - k]) at the index where column j has Z[k])
+          const C2 c = v[20 - j];
+          store(20 - j, {fma_f32x2(c.re, tr, mul_f32x2(c.im, ti)), sub_f32x2(mul_f32x2(c.re, ti), mul_f32x2(c.im, tr))});
         }
       }
-      __syncthreads();
-      float* p = reinterpret_cast<float*>(sm.ez) + lane20 * kPRow + 2 * fft;   // P[k][frame]
-#pragma unroll
-      for (int j = 0; j < 11; ++j)
-        if (j < 10 || lane20 == 0) { p[20 * j * kPRow] = pa[j]; p[20 * j * kPRow + 1] = pb[j]; }
     }
     __syncthreads();
-    // ---- banded mel projection (lane = frame), log10, per-tile statistics ----------------------
-    // rows 201..203 of P are whatever Z left there (finite); the weights beyond a band are zero.
+    // ---- pass 2: columns (task, 20 - task) [task 0: columns 0 and 10] in the two slots; DFT over n2 ----------------------
+    {
+      const int bx = task, by = task == 0 ? 10 : 20 - task;
+#pragma unroll
+      for (int n2 = 0; n2 < 20; ++n2) {
+        const int pos = (n2 >> 1) + 10 * (n2 & 1);
+        v[n2].re = pack_f32x2(sm.e_re[e_index(bx, pos, fft)], sm.e_re[e_index(by, pos, fft)]);
+        v[n2].im = pack_f32x2(sm.e_im[e_index(bx, pos, fft)], sm.e_im[e_index(by, pos, fft)]);
+      }
+      dft20(v);
+      // power rows P[bin][frame]; odd bins keep their two 16-frame halves exchanged (the two tasks of a half warp write
+      // neighbouring bins: they land in different banks)
+      float* pw = reinterpret_cast<float*>(sm.slot[buf]);
+      if (task != 0) {
+        // slot x: Z[k], k = task + 20 k2; slot y: conj(Z[400 - k])
+        float2* prow = reinterpret_cast<float2*>(pw + ((2 * fft) ^ ((task & 1) << 4)));
+#pragma unroll
+        for (int k2 = 0; k2 < 20; ++k2) {
+          float xr, yr, xi, yi;
+          unpack_f32x2(v[k2].re, xr, yr);
+          unpack_f32x2(v[k2].im, xi, yi);
+          const uint64_t u = pack_f32x2(xr + yr, xr - yr), w = pack_f32x2(xi + yi, xi - yi);
+          const uint64_t p = fma_f32x2(w, w, mul_f32x2(u, u));      // (|2 X_A|^2, |2 X_B|^2)
+          const int bin_off = k2 <= 9 ? 20 * k2 : 20 * (19 - k2) + 20;   // bin = +task or -task from here
+          float2* dst = k2 <= 9 ? prow + (bin_off + task) * (kPRow / 2) : prow + (bin_off - task) * (kPRow / 2);
+          *reinterpret_cast<uint64_t*>(dst) = p;
+        }
+      } else {
+        // columns 0 (slot x) and 10 (slot y) are their own partners
+        float zr0[20], zi0[20], zr1[20], zi1[20];
+#pragma unroll
+        for (int k2 = 0; k2 < 20; ++k2) { unpack_f32x2(v[k2].re, zr0[k2], zr1[k2]); unpack_f32x2(v[k2].im, zi0[k2], zi1[k2]); }
+        float2* p_even = reinterpret_cast<float2*>(pw + 2 * fft);     // bins 20 k2 and 10 + 20 k2 are all even
+#pragma unroll
+        for (int k2 = 0; k2 <= 10; ++k2) {
+          const int kb = (20 - k2) % 20;
+          p_even[(20 * k2) * (kPRow / 2)] = untangle_power(zr0[k2], zi0[k2], zr0[kb], zi0[kb]);
+        }
+#pragma unroll
+        for (int k2 = 0; k2 < 10; ++k2)
+          p_even[(10 + 20 * k2) * (kPRow / 2)] = untangle_power(zr1[k2], zi1[k2], zr1[19 - k2], zi1[19 - k2]);
+      }
+    }
+    __syncthreads();
+    // ---- banded mel projection (lane = frame pair, two bands per warp), log10, per-tile statistics ----------------------
     float acc_sum = 0.0f, acc_sq = 0.0f, acc_max = -INFINITY;
     const int frame0 = tile * kFramesPerCta;
-    const float* power = reinterpret_cast<const float*>(sm.ez);
-    float* otile = reinterpret_cast<float*>(sm.ez) + kPRows * kPRow;          // [frame][o_stride]
-    const bool lane_valid = frame0 + lane < n_frames;
-    for (int round = 0; round < sched.rounds; ++round) {
-      const int r = round * kWarps + ((round & 1) ? kWarps - 1 - warp : warp);
-      const int n4 = sched.n4[round];                                         // the same for every warp: a uniform loop
-      if (r < n_mels) {
-        const int2 band = sm.mel_band[r];                                     // {mel row, first bin}
-        const float* pk = power + band.y * kPRow + lane;
-        const float4* w4 = reinterpret_cast<const float4*>(sm.mel_w + r * band_stride);
-        float a0 = 0.0f, a1 = 0.0f;
-#pragma unroll 1
-        for (int i = 0; i < n4; ++i) {
-          const float4 w = w4[i];
-          a0 = fmaf(w.x, pk[0], a0);
-          a1 = fmaf(w.y, pk[kPRow], a1);
-          a0 = fmaf(w.z, pk[2 * kPRow], a0);
-          a1 = fmaf(w.w, pk[3 * kPRow], a1);
-          pk += 4 * kPRow;
-        }
-        float val = a0 + a1;
-        if (norm != YOHO_NORM_NONE) {
-          val = lg2_approx(fmaxf(val, log_floor)) * 0.30102999566398120f;     // the floor keeps the argument normal
-          if (lane_valid) {
-            acc_sum += val;
-            acc_sq = fmaf(val, val, acc_sq);
-            acc_max = fmaxf(acc_max, val);
+    // output tile [mel][32 frames]; E is dead: every thread loaded its rows before the barrier
+    float* otile = sm.e_re;
+    {
+      const uint32_t pbase = ptx::smem_u32(sm.slot[buf]), wbase = ptx::smem_u32(sm.mel_w);
+      const uint32_t col_even = uint32_t(2 * fp) * 4u, col_odd = uint32_t((2 * fp) ^ 16) * 4u;   // odd bins keep their halves exchanged
+      const bool valid0 = frame0 + 2 * fp < n_frames, valid1 = frame0 + 2 * fp + 1 < n_frames;
+      for (int round = 0; round * kWarps < n_pairs; ++round) {
+        const int pi = round * kWarps + ((round & 1) ? kWarps - 1 - warp : warp);     // longest first, boustrophedon
+        if (pi >= n_pairs) break;
+        const int4 band = sm.mel_band[2 * pi + mh];             // {mel row, first bin, weight offset, trip}
+        const bool odd = band.y & 1;
+        const uint32_t a0 = pbase + uint32_t(band.y) * (kPRow * 4) + (odd ? col_odd : col_even);
+        const uint32_t a1 = pbase + uint32_t(band.y + 1) * (kPRow * 4) + (odd ? col_even : col_odd);
+        const uint32_t wa = wbase + uint32_t(band.z) * 8u;
+        const int steps = band.w >> 1;                          // two bins a step; the same for both bands of the pair
+        // one straight-line variant per step count (bands of the reference filterbanks have at most 14 bins): all loads
+        // first with immediate offsets, then the two accumulation chains; no loop bookkeeping, one uniform branch
+        uint64_t sum;
+        switch (steps) {
+          case 0: sum = 0ull; break;
+          case 1: sum = mel_pair<1>(a0, a1, wa); break;
+          case 2: sum = mel_pair<2>(a0, a1, wa); break;
+          case 3: sum = mel_pair<3>(a0, a1, wa); break;
+          case 4: sum = mel_pair<4>(a0, a1, wa); break;
+          case 5: sum = mel_pair<5>(a0, a1, wa); break;
+          case 6: sum = mel_pair<6>(a0, a1, wa); break;
+          case 7: sum = mel_pair<7>(a0, a1, wa); break;
+          default: {                                            // longer bands (other filterbanks): chunks of seven steps, then the rest
+            sum = 0ull;
+            int done = 0;
+            for (; done + 7 <= steps; done += 7)
+              sum = add_f32x2(sum, mel_pair<7>(a0 + uint32_t(done) * (2 * kPRow * 4), a1 + uint32_t(done) * (2 * kPRow * 4), wa + uint32_t(done) * 16u));
+            for (; done < steps; ++done)
+              sum = add_f32x2(sum, mel_pair<1>(a0 + uint32_t(done) * (2 * kPRow * 4), a1 + uint32_t(done) * (2 * kPRow * 4), wa + uint32_t(done) * 16u));
           }
         }
-        otile[lane * o_stride + band.x] = val;
+        float v0, v1;
+        unpack_f32x2(sum, v0, v1);
+        if (kNorm != YOHO_NORM_NONE) {
+          v0 = lg2_approx(fmaxf(v0, log_floor)) * 0.30102999566398120f;     // the floor keeps the argument normal
+          v1 = lg2_approx(fmaxf(v1, log_floor)) * 0.30102999566398120f;
+          if (band.x >= 0) {
+            if (kNorm == YOHO_NORM_REFERENCE) {
+              if (valid0) { acc_sum += v0; acc_sq = fmaf(v0, v0, acc_sq); }
+              if (valid1) { acc_sum += v1; acc_sq = fmaf(v1, v1, acc_sq); }
+            } else {
+              if (valid0) acc_max = fmaxf(acc_max, v0);
+              if (valid1) acc_max = fmaxf(acc_max, v1);
+            }
+          }
+        }
+        if (band.x >= 0) *reinterpret_cast<float2*>(otile + band.x * kFramesPerCta + 2 * fp) = make_float2(v0, v1);
       }
     }
-    if (norm != YOHO_NORM_NONE) {
-      float a = (norm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sum) : warp_max(acc_max);
-      float b = (norm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sq) : 0.0f;
+    if (kNorm != YOHO_NORM_NONE) {
+      float a = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sum) : warp_max(acc_max);
+      float b = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sq) : 0.0f;
       if (lane == 0) { sm.red[warp] = a; sm.red[32 + warp] = b; }
     }
     __syncthreads();
-    // ---- the tile's (frames, n_mels) block is contiguous in `out`: full-line stores ----------------
+    // ---- the tile's (frames, n_mels) block is contiguous in `out` ----------------------------------------------------
     {
       float* out_tile = out + (size_t(clip) * n_frames + frame0) * n_mels;
       const int rows = min(kFramesPerCta, n_frames - frame0);
-      for (int f = warp; f < rows; f += kWarps)
-        for (int m = lane; m < n_mels; m += 32) out_tile[f * n_mels + m] = otile[f * o_stride + m];
+      if (vec_out) {
+        // item = (4 mels) x (4 frames): four 128-bit reads along the frames, transposed in registers (by naming), four
+        // 128-bit stores along the mels; consecutive lanes take consecutive frame groups (conflict-free reads) and
+        // every 32-byte sector of `out` is written whole
+        const int items = (n_mels >> 2) * 8;
+        for (int idx = tid; idx < items; idx += kThreads) {
+          const int f4 = idx & 7, m4 = idx >> 3;
+          const float4* src = reinterpret_cast<const float4*>(otile + (4 * m4) * kFramesPerCta + 4 * f4);
+          const float4 r0 = src[0], r1 = src[kFramesPerCta / 4], r2 = src[2 * (kFramesPerCta / 4)], r3 = src[3 * (kFramesPerCta / 4)];
+          float* dst = out_tile + size_t(4 * f4) * n_mels + 4 * m4;
+          if (4 * f4 + 0 < rows) *reinterpret_cast<float4*>(dst) = make_float4(r0.x, r1.x, r2.x, r3.x);
+          if (4 * f4 + 1 < rows) *reinterpret_cast<float4*>(dst + n_mels) = make_float4(r0.y, r1.y, r2.y, r3.y);
+          if (4 * f4 + 2 < rows) *reinterpret_cast<float4*>(dst + 2 * n_mels) = make_float4(r0.z, r1.z, r2.z, r3.z);
+          if (4 * f4 + 3 < rows) *reinterpret_cast<float4*>(dst + 3 * n_mels) = make_float4(r0.w, r1.w, r2.w, r3.w);
+        }
+      } else {
+        for (int f = warp; f < rows; f += kWarps)
+          for (int m = lane; m < n_mels; m += 32) out_tile[f * n_mels + m] = otile[m * kFramesPerCta + f];
+      }
     }
-    if (norm != YOHO_NORM_NONE && warp == 0) {
+    if (kNorm != YOHO_NORM_NONE && warp == 0) {
       float a, b;
-      if (norm == YOHO_NORM_REFERENCE) {
+      if (kNorm == YOHO_NORM_REFERENCE) {
         a = warp_sum(lane < kWarps ? sm.red[lane] : 0.0f);
         b = warp_sum(lane < kWarps ? sm.red[32 + lane] : 0.0f);
       } else {
@@ -323,6 +481,36 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
       if (lane == 0) stats[size_t(clip) * tiles_per_clip + tile] = make_float2(a, b);
     }
   }
+}
+
+// ---- constant tables ------------------------------------------------------------------------------------------------
+int frontend_upload_constants(double* window_sum) {
+  // Periodic Hann, scipy.signal.get_window('hann', 400): float64 then rounded to float32, exactly what
+  // jax.scipy.signal.stft multiplies by (reference audio.py:33).
+  const double kPi = 3.14159265358979323846;
+  std::vector<float> win(400);
+  double wsum = 0.0;
+  for (int n = 0; n < 400; ++n) {
+    win[n] = float(0.5 - 0.5 * std::cos(2.0 * kPi * n / 400.0));
+    wsum += double(win[n]);
+  }
+  *window_sum = wsum;
+  static float2 h_win[2][10][20];
+  static float4 h_tw[10][11];
+  for (int t = 0; t < 10; ++t) {
+    for (int n1 = 0; n1 < 20; ++n1) {
+      const float a = win[20 * n1 + 2 * t], b = win[20 * n1 + 2 * t + 1];
+      h_win[0][t][n1] = make_float2(a, b);
+      h_win[1][t][n1] = make_float2(a * (1.0f / 32768.0f), b * (1.0f / 32768.0f));   // exact (power of two)
+    }
+    for (int j = 0; j <= 10; ++j) {
+      const double a0 = -2.0 * kPi * double(2 * t * j) / 400.0, a1 = -2.0 * kPi * double((2 * t + 1) * j) / 400.0;
+      h_tw[t][j] = make_float4(float(std::cos(a0)), float(std::cos(a1)), float(std::sin(a0)), float(std::sin(a1)));
+    }
+  }
+  YOHO_CUDA_CHECK(cudaMemcpyToSymbol(c_win, h_win, sizeof(h_win)));
+  YOHO_CUDA_CHECK(cudaMemcpyToSymbol(c_tw, h_tw, sizeof(h_tw)));
+  return YOHO_OK;
 }
 
 // ---- per-clip statistics of an existing mel power spectrogram (stand-alone normaliser) -------
@@ -454,7 +642,7 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
   if (norm < YOHO_NORM_NONE || norm > YOHO_NORM_WHISPER) return fail(YOHO_ERR_INVALID, "yoho_logmel: norm=%d", norm);
   if (n_fft != kNfft || hop != kHop)
     return fail(YOHO_ERR_UNSUPPORTED, "yoho_logmel: kernels exist for n_fft=400, hop=160 (got %d, %d)", n_fft, hop);
-  if (fb->n_mels > kMaxMels) return fail(YOHO_ERR_UNSUPPORTED, "yoho_logmel: n_mels=%d, the kernel's output tile holds up to %d", fb->n_mels, kMaxMels);
+  if (fb->n_mels > kMelMaxBands) return fail(YOHO_ERR_UNSUPPORTED, "yoho_logmel: n_mels=%d, the kernel's output tile holds up to %d", fb->n_mels, kMelMaxBands);
   if (fb->n_bins != kBins) return fail(YOHO_ERR_INVALID, "yoho_logmel: filterbank has %d bins, n_fft=400 needs 201", fb->n_bins);
   if (fb->device != ctx->device) return fail(YOHO_ERR_INVALID, "yoho_logmel: filterbank lives on device %d, context on %d", fb->device, ctx->device);
   int frames = frames_of(n_samples, n_fft, hop);
@@ -464,11 +652,16 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
   if (norm != YOHO_NORM_NONE && (ws == nullptr || ws_bytes < need))
     return fail(YOHO_ERR_WORKSPACE, "yoho_logmel: workspace %zu < %zu bytes", ws_bytes, need);
 
-  static_assert(sizeof(FrontendSmem<T>) <= 113 * 1024, "two CTAs per SM");
-  YOHO_CUDA_CHECK(cudaFuncSetAttribute(logmel_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FrontendSmem<T>))));
+  static_assert(2 * (sizeof(FrontendSmem<T>) + 1024) <= 228 * 1024, "two CTAs per SM");
+  auto kernel = norm == YOHO_NORM_NONE ? logmel_kernel<T, YOHO_NORM_NONE>
+                : norm == YOHO_NORM_REFERENCE ? logmel_kernel<T, YOHO_NORM_REFERENCE> : logmel_kernel<T, YOHO_NORM_WHISPER>;
+  YOHO_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(FrontendSmem<T>))));
+  // two CTAs of ~113 KB need the full 228 KB carve-out; left to itself the driver may size it for one
+  YOHO_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
   const int tiles = logmel_tiles(frames);
   float2* stats = static_cast<float2*>(ws);
   const int vec_ok = (n_samples % int(16 / sizeof(T)) == 0) && (reinterpret_cast<uintptr_t>(pcm) % 16 == 0);
+  const int vec_out = (fb->n_mels % 4 == 0) && (reinterpret_cast<uintptr_t>(out) % 16 == 0);
   const int elems = frames * fb->n_mels;
   const int chunk = (norm == YOHO_NORM_NONE) ? 65535 : clips_per_chunk(frames, fb->n_mels);
   for (int c0 = 0; c0 < batch; c0 += chunk) {
@@ -477,9 +670,9 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
       ProfScope prof(stream, kProfFrontend, double(nb) * (double(n_samples) * sizeof(T) + double(elems) * sizeof(float)));
       const long long items = (long long)nb * tiles;
       const int grid = int(items < 2LL * ctx->num_sms ? items : 2LL * ctx->num_sms);
-      logmel_kernel<T><<<grid, kThreads, sizeof(FrontendSmem<T>), stream>>>(
-          pcm, n_samples, total_samples, frames, c0, int(items), ctx->d_window, ctx->d_twiddle, fb->d_bands, fb->d_weights,
-          fb->band_stride, fb->n_mels, fb->sched, out, stats, tiles, norm, vec_ok);
+      kernel<<<grid, kThreads, sizeof(FrontendSmem<T>), stream>>>(
+          pcm, n_samples, total_samples, frames, c0, int(items), fb->d_bands, fb->d_weights, fb->n_pairs, fb->n_weights,
+          fb->n_mels, out, stats, tiles, vec_ok, vec_out);
       YOHO_LAUNCH_CHECK("logmel_kernel");
     }
     if (norm != YOHO_NORM_NONE) {
