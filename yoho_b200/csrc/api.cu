@@ -177,15 +177,16 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return len[a] > len[b]; });
   // |2 X[k]|^2 comes out of the packed-pair FFT; stft scales by 1/sum(w) (scaling='spectrum').
   const double scale = 0.25 / (ctx->window_sum * ctx->window_sum);
-  const int n_pairs = (n_mels + 1) / 2;
-  std::vector<int4> bands(size_t(2) * n_pairs);
+  // groups of four bands (longest first) share one trip count: a warp walks two bands per half warp at a time
+  const int n_groups = (n_mels + kMelGroup - 1) / kMelGroup;
+  std::vector<int4> bands(size_t(kMelGroup) * n_groups);
   std::vector<float2> w;
-  for (int p = 0; p < n_pairs; ++p) {
-    const int trip = (len[order[2 * p]] + 1) & ~1;                 // the pair's longer band comes first; walked two bins a step
-    if (trip > n_bins - (n_bins & 1)) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: band of %d bins", len[order[2 * p]]);
-    for (int h = 0; h < 2; ++h) {
-      const int r = 2 * p + h;
-      if (r >= n_mels) { bands[r] = make_int4(-1, 0, int(w.size()) - trip, trip); continue; }   // odd n_mels: walks the partner's weights, stores nothing
+  for (int g = 0; g < n_groups; ++g) {
+    const int trip = (len[order[kMelGroup * g]] + 1) & ~1;        // the group's longest band comes first; walked two bins a step
+    if (trip > n_bins - (n_bins & 1)) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: band of %d bins", len[order[kMelGroup * g]]);
+    for (int h = 0; h < kMelGroup; ++h) {
+      const int r = kMelGroup * g + h;
+      if (r >= n_mels) { bands[r] = make_int4(-1, 0, int(w.size()) - trip, trip); continue; }   // filler: walks its neighbour's weights, stores nothing
       const int m = order[r];
       const int first = lo[m] + trip <= n_bins ? lo[m] : n_bins - trip;   // keep the walk inside the power tile
       bands[r] = make_int4(m, first, int(w.size()), trip);
@@ -204,7 +205,7 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
   fb->device = ctx->device;
   fb->n_mels = n_mels;
   fb->n_bins = n_bins;
-  fb->n_pairs = n_pairs;
+  fb->n_groups = n_groups;
   fb->n_weights = int(w.size());
   fb->power_scale = scale;
   cudaError_t e;

@@ -78,17 +78,18 @@ int frontend_upload_constants(double* window_sum);
 }
 
 // Mel filterbank as the log-mel kernel consumes it.  Every mel row is a band [first, first + trip) of FFT bins; bands are
-// sorted longest first and taken two at a time (one per half warp, lane = frame pair), so both bands of a pair are walked
-// `trip` bins (the longer one's length rounded up to even) with zero weights past their own end.
+// sorted longest first and taken four at a time (two per half warp, lane = frame pair), so the bands of a group are all
+// walked `trip` bins (the longest one's length rounded up to even) with zero weights past their own end.
 constexpr int kMelMaxBands = 128;      // n_mels <= 128 (band pairs * 2)
 constexpr int kMelMaxWeights = 600;    // (w, w) entries held in shared memory: sum over bands of their pair's trip
 constexpr int kMelBins = 201;          // n_fft / 2 + 1
+constexpr int kMelGroup = 4;           // bands that share a trip count (two per half warp, interleaved)
 struct yoho_filterbank {
   int device = -1;
   int n_mels = 0, n_bins = 0;
-  int n_pairs = 0;            // band pairs, sorted by trip (descending)
+  int n_groups = 0;           // groups of kMelGroup bands, sorted by trip (descending)
   int n_weights = 0;          // float2 entries in d_weights
-  int4* d_bands = nullptr;    // [2 * n_pairs] {mel row or -1, first bin walked, offset into d_weights, trip}
+  int4* d_bands = nullptr;    // [kMelGroup * n_groups] {mel row or -1, first bin walked, offset into d_weights, trip}
   float2* d_weights = nullptr; // (w, w) per walked bin, already multiplied by the STFT power scale
   double power_scale = 0.0;   // 0.25 / window_sum^2 folded into d_weights
 };

@@ -226,25 +226,35 @@ __device__ __forceinline__ void stage_pcm_async(T* dst, const T* __restrict__ pc
 // E[block][pos][fft]: the element of column n2 sits at row block * 21 + pos(n2), pos = n2 / 2 + 10 * (n2 & 1)
 __device__ __forceinline__ int e_index(int block, int pos, int fft) { return (block * kEBlockRows + pos) * kFftsPerCta + fft; }
 
-// Two bands' worth (one per half warp) of kSteps x 2 bins for one frame pair: sum_i P[first + i][frames] * w_i.  a0 / a1
-// address the even / odd steps' rows (odd bins keep their 16-frame halves exchanged), wa the (w, w) table.
+// One frame pair against two bands (this half warp's two bands of a group; the other half warp has the other two):
+// sum_i P[first + i][frames] * w_i over kSteps x 2 bins each.  a0 / a1 address the even / odd steps' rows of a band (odd
+// bins keep their 16-frame halves exchanged), wa its (w, w) table.  All loads first, with immediate offsets; four
+// independent accumulation chains.
+struct MelBandAddr { uint32_t a0, a1, wa; };
 template <int kSteps>
-__device__ __forceinline__ uint64_t mel_pair(uint32_t a0, uint32_t a1, uint32_t wa) {
-  uint64_t p0[kSteps], p1[kSteps];
-  float4 w[kSteps];
+__device__ __forceinline__ void mel_quad(const MelBandAddr& x, const MelBandAddr& y, uint64_t& sum_x, uint64_t& sum_y) {
+  uint64_t xp0[kSteps], xp1[kSteps], yp0[kSteps], yp1[kSteps];
+  float4 xw[kSteps], yw[kSteps];
 #pragma unroll
   for (int i = 0; i < kSteps; ++i) {
-    p0[i] = lds_u64(a0 + uint32_t(i) * (2 * kPRow * 4));
-    p1[i] = lds_u64(a1 + uint32_t(i) * (2 * kPRow * 4));
-    w[i] = lds_f4(wa + uint32_t(i) * 16u);                    // (w_2i, w_2i, w_2i+1, w_2i+1)
+    xp0[i] = lds_u64(x.a0 + uint32_t(i) * (2 * kPRow * 4));
+    xp1[i] = lds_u64(x.a1 + uint32_t(i) * (2 * kPRow * 4));
+    xw[i] = lds_f4(x.wa + uint32_t(i) * 16u);                 // (w_2i, w_2i, w_2i+1, w_2i+1)
+    yp0[i] = lds_u64(y.a0 + uint32_t(i) * (2 * kPRow * 4));
+    yp1[i] = lds_u64(y.a1 + uint32_t(i) * (2 * kPRow * 4));
+    yw[i] = lds_f4(y.wa + uint32_t(i) * 16u);
   }
-  uint64_t s0 = mul_f32x2(p0[0], pack_f32x2(w[0].x, w[0].y)), s1 = mul_f32x2(p1[0], pack_f32x2(w[0].z, w[0].w));
+  uint64_t s0 = mul_f32x2(xp0[0], pack_f32x2(xw[0].x, xw[0].y)), s1 = mul_f32x2(xp1[0], pack_f32x2(xw[0].z, xw[0].w));
+  uint64_t t0 = mul_f32x2(yp0[0], pack_f32x2(yw[0].x, yw[0].y)), t1 = mul_f32x2(yp1[0], pack_f32x2(yw[0].z, yw[0].w));
 #pragma unroll
   for (int i = 1; i < kSteps; ++i) {
-    s0 = fma_f32x2(p0[i], pack_f32x2(w[i].x, w[i].y), s0);
-    s1 = fma_f32x2(p1[i], pack_f32x2(w[i].z, w[i].w), s1);
+    s0 = fma_f32x2(xp0[i], pack_f32x2(xw[i].x, xw[i].y), s0);
+    s1 = fma_f32x2(xp1[i], pack_f32x2(xw[i].z, xw[i].w), s1);
+    t0 = fma_f32x2(yp0[i], pack_f32x2(yw[i].x, yw[i].y), t0);
+    t1 = fma_f32x2(yp1[i], pack_f32x2(yw[i].z, yw[i].w), t1);
   }
-  return add_f32x2(s0, s1);
+  sum_x = add_f32x2(sum_x, add_f32x2(s0, s1));
+  sum_y = add_f32x2(sum_y, add_f32x2(t0, t1));
 }
 
 // |2 X_A[k]|^2 and |2 X_B[k]|^2 from a = Z[k], b = Z[400 - k] (frames A, B packed as re / im of one complex FFT)
@@ -258,7 +268,7 @@ __device__ __forceinline__ float2 untangle_power(float ax, float ay, float bx, f
 template <typename T, int kNorm>
 __global__ void __launch_bounds__(kThreads, 2)
 logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples, int n_frames, int clip0, int n_items,
-              const int4* __restrict__ fb_bands, const float2* __restrict__ fb_w, int n_pairs, int n_weights, int n_mels,
+              const int4* __restrict__ fb_bands, const float2* __restrict__ fb_w, int n_groups, int n_weights, int n_mels,
               float* __restrict__ out, float2* __restrict__ stats, int tiles_per_clip, int vec_ok, int vec_out) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   using Smem = FrontendSmem<T>;
@@ -289,12 +299,28 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
   for (int i = tid; i < 10 * 11; i += kThreads) (&sm.tw[0][0])[i] = (&c_tw[0][0])[i];
   for (int i = tid; i < 10 * 20; i += kThreads) (&sm.win[0][0])[i] = (&c_win[kWin][0][0])[i];
   for (int i = tid; i < n_weights; i += kThreads) sm.mel_w[i] = __ldg(fb_w + i);
-  for (int i = tid; i < 2 * n_pairs; i += kThreads) sm.mel_band[i] = __ldg(fb_bands + i);
+  for (int i = tid; i < kMelGroup * n_groups; i += kThreads) sm.mel_band[i] = __ldg(fb_bands + i);
+
+  // statistics of the tile finished last: its per-warp partials sit in red[]; warp 0 adds them once a barrier has passed
+  int pending_stats = -1;
+  auto write_stats = [&]() {
+    if (warp != 0 || pending_stats < 0) return;
+    float a, b;
+    if (kNorm == YOHO_NORM_REFERENCE) {
+      a = warp_sum(lane < kWarps ? sm.red[lane] : 0.0f);
+      b = warp_sum(lane < kWarps ? sm.red[32 + lane] : 0.0f);
+    } else {
+      a = warp_max(lane < kWarps ? sm.red[lane] : -INFINITY);
+      b = 0.0f;
+    }
+    if (lane == 0) stats[pending_stats] = make_float2(a, b);
+  };
 
   for (int buf = 0; item < n_items; item += gridDim.x, buf ^= 1) {
     const int clip = clip0 + item / tiles_per_clip, tile = item % tiles_per_clip;
     cp_async_wait_all();
-    __syncthreads();  // this tile's samples have landed; the previous tile's power rows (other slot), output tile and red[] are free
+    __syncthreads();  // this tile's samples have landed; the previous tile's power rows (other slot), output tile and red[] are complete
+    if (kNorm != YOHO_NORM_NONE) write_stats();
     if (item + int(gridDim.x) < n_items) stage(item + gridDim.x, buf ^ 1);
     cp_async_commit();
 
@@ -382,71 +408,66 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
       }
     }
     __syncthreads();
-    // ---- banded mel projection (lane = frame pair, two bands per warp), log10, per-tile statistics ----------------------
-    float acc_sum = 0.0f, acc_sq = 0.0f, acc_max = -INFINITY;
+    // ---- banded mel projection: lane = frame pair, four bands per warp and step (two per half warp, interleaved) -------
     const int frame0 = tile * kFramesPerCta;
-    // output tile [mel][32 frames]; E is dead: every thread loaded its rows before the barrier
+    // output tile [mel][32 frames] of mel POWER; E is dead: every thread loaded its rows before the barrier
     float* otile = sm.e_re;
     {
       const uint32_t pbase = ptx::smem_u32(sm.slot[buf]), wbase = ptx::smem_u32(sm.mel_w);
       const uint32_t col_even = uint32_t(2 * fp) * 4u, col_odd = uint32_t((2 * fp) ^ 16) * 4u;   // odd bins keep their halves exchanged
-      const bool valid0 = frame0 + 2 * fp < n_frames, valid1 = frame0 + 2 * fp + 1 < n_frames;
-      for (int round = 0; round * kWarps < n_pairs; ++round) {
-        const int pi = round * kWarps + ((round & 1) ? kWarps - 1 - warp : warp);     // longest first, boustrophedon
-        if (pi >= n_pairs) break;
-        const int4 band = sm.mel_band[2 * pi + mh];             // {mel row, first bin, weight offset, trip}
+      auto address = [&](const int4& band) {
         const bool odd = band.y & 1;
-        const uint32_t a0 = pbase + uint32_t(band.y) * (kPRow * 4) + (odd ? col_odd : col_even);
-        const uint32_t a1 = pbase + uint32_t(band.y + 1) * (kPRow * 4) + (odd ? col_even : col_odd);
-        const uint32_t wa = wbase + uint32_t(band.z) * 8u;
-        const int steps = band.w >> 1;                          // two bins a step; the same for both bands of the pair
-        // one straight-line variant per step count (bands of the reference filterbanks have at most 14 bins): all loads
-        // first with immediate offsets, then the two accumulation chains; no loop bookkeeping, one uniform branch
-        uint64_t sum;
+        return MelBandAddr{pbase + uint32_t(band.y) * (kPRow * 4) + (odd ? col_odd : col_even),
+                           pbase + uint32_t(band.y + 1) * (kPRow * 4) + (odd ? col_even : col_odd), wbase + uint32_t(band.z) * 8u};
+      };
+      auto group_of = [&](int round) { return round * kWarps + ((round & 1) ? kWarps - 1 - warp : warp); };   // longest first, boustrophedon
+      // descriptors {mel row, first bin, weight offset, trip} are fetched one round ahead
+      int4 nx = sm.mel_band[kMelGroup * min(group_of(0), n_groups - 1) + mh], ny = sm.mel_band[kMelGroup * min(group_of(0), n_groups - 1) + 2 + mh];
+      for (int round = 0; round * kWarps < n_groups; ++round) {
+        const int gi = group_of(round);
+        if (gi >= n_groups) break;
+        const int4 bx = nx, by = ny;
+        {
+          const int gn = min(group_of(round + 1), n_groups - 1);
+          nx = sm.mel_band[kMelGroup * gn + mh];
+          ny = sm.mel_band[kMelGroup * gn + 2 + mh];
+        }
+        MelBandAddr ax = address(bx), ay = address(by);
+        int steps = bx.w >> 1;                                  // two bins a step; the same for the four bands of the group
+        uint64_t sum_x = 0ull, sum_y = 0ull;
+        // one straight-line variant per step count (bands of the reference filterbanks have at most 14 bins); longer
+        // bands (other filterbanks) take chunks of seven steps first
+        while (steps > 7) {
+          mel_quad<7>(ax, ay, sum_x, sum_y);
+          ax.a0 += 7 * 2 * kPRow * 4; ax.a1 += 7 * 2 * kPRow * 4; ax.wa += 7 * 16;
+          ay.a0 += 7 * 2 * kPRow * 4; ay.a1 += 7 * 2 * kPRow * 4; ay.wa += 7 * 16;
+          steps -= 7;
+        }
         switch (steps) {
-          case 0: sum = 0ull; break;
-          case 1: sum = mel_pair<1>(a0, a1, wa); break;
-          case 2: sum = mel_pair<2>(a0, a1, wa); break;
-          case 3: sum = mel_pair<3>(a0, a1, wa); break;
-          case 4: sum = mel_pair<4>(a0, a1, wa); break;
-          case 5: sum = mel_pair<5>(a0, a1, wa); break;
-          case 6: sum = mel_pair<6>(a0, a1, wa); break;
-          case 7: sum = mel_pair<7>(a0, a1, wa); break;
-          default: {                                            // longer bands (other filterbanks): chunks of seven steps, then the rest
-            sum = 0ull;
-            int done = 0;
-            for (; done + 7 <= steps; done += 7)
-              sum = add_f32x2(sum, mel_pair<7>(a0 + uint32_t(done) * (2 * kPRow * 4), a1 + uint32_t(done) * (2 * kPRow * 4), wa + uint32_t(done) * 16u));
-            for (; done < steps; ++done)
-              sum = add_f32x2(sum, mel_pair<1>(a0 + uint32_t(done) * (2 * kPRow * 4), a1 + uint32_t(done) * (2 * kPRow * 4), wa + uint32_t(done) * 16u));
-          }
+          case 1: mel_quad<1>(ax, ay, sum_x, sum_y); break;
+          case 2: mel_quad<2>(ax, ay, sum_x, sum_y); break;
+          case 3: mel_quad<3>(ax, ay, sum_x, sum_y); break;
+          case 4: mel_quad<4>(ax, ay, sum_x, sum_y); break;
+          case 5: mel_quad<5>(ax, ay, sum_x, sum_y); break;
+          case 6: mel_quad<6>(ax, ay, sum_x, sum_y); break;
+          case 7: mel_quad<7>(ax, ay, sum_x, sum_y); break;
+          default: break;
         }
-        float v0, v1;
-        unpack_f32x2(sum, v0, v1);
-        if (kNorm != YOHO_NORM_NONE) {
-          v0 = lg2_approx(fmaxf(v0, log_floor)) * 0.30102999566398120f;     // the floor keeps the argument normal
-          v1 = lg2_approx(fmaxf(v1, log_floor)) * 0.30102999566398120f;
-          if (band.x >= 0) {
-            if (kNorm == YOHO_NORM_REFERENCE) {
-              if (valid0) { acc_sum += v0; acc_sq = fmaf(v0, v0, acc_sq); }
-              if (valid1) { acc_sum += v1; acc_sq = fmaf(v1, v1, acc_sq); }
-            } else {
-              if (valid0) acc_max = fmaxf(acc_max, v0);
-              if (valid1) acc_max = fmaxf(acc_max, v1);
-            }
-          }
-        }
-        if (band.x >= 0) *reinterpret_cast<float2*>(otile + band.x * kFramesPerCta + 2 * fp) = make_float2(v0, v1);
+        if (bx.x >= 0) *reinterpret_cast<uint64_t*>(otile + bx.x * kFramesPerCta + 2 * fp) = sum_x;
+        if (by.x >= 0) *reinterpret_cast<uint64_t*>(otile + by.x * kFramesPerCta + 2 * fp) = sum_y;
       }
     }
-    if (kNorm != YOHO_NORM_NONE) {
-      float a = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sum) : warp_max(acc_max);
-      float b = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sq) : 0.0f;
-      if (lane == 0) { sm.red[warp] = a; sm.red[32 + warp] = b; }
-    }
     __syncthreads();
-    // ---- the tile's (frames, n_mels) block is contiguous in `out` ----------------------------------------------------
+    // ---- log10, per-tile statistics and the stores: the tile's (frames, n_mels) block is contiguous in `out` -----------
     {
+      float acc_sum = 0.0f, acc_sq = 0.0f, acc_max = -INFINITY;
+      auto finish = [&](float v, bool valid) {
+        if (kNorm == YOHO_NORM_NONE) return v;
+        v = lg2_approx(fmaxf(v, log_floor)) * 0.30102999566398120f;      // the floor keeps the argument normal
+        if (kNorm == YOHO_NORM_REFERENCE) { if (valid) { acc_sum += v; acc_sq = fmaf(v, v, acc_sq); } }
+        else if (valid) acc_max = fmaxf(acc_max, v);
+        return v;
+      };
       float* out_tile = out + (size_t(clip) * n_frames + frame0) * n_mels;
       const int rows = min(kFramesPerCta, n_frames - frame0);
       if (vec_out) {
@@ -459,27 +480,32 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
           const float4* src = reinterpret_cast<const float4*>(otile + (4 * m4) * kFramesPerCta + 4 * f4);
           const float4 r0 = src[0], r1 = src[kFramesPerCta / 4], r2 = src[2 * (kFramesPerCta / 4)], r3 = src[3 * (kFramesPerCta / 4)];
           float* dst = out_tile + size_t(4 * f4) * n_mels + 4 * m4;
-          if (4 * f4 + 0 < rows) *reinterpret_cast<float4*>(dst) = make_float4(r0.x, r1.x, r2.x, r3.x);
-          if (4 * f4 + 1 < rows) *reinterpret_cast<float4*>(dst + n_mels) = make_float4(r0.y, r1.y, r2.y, r3.y);
-          if (4 * f4 + 2 < rows) *reinterpret_cast<float4*>(dst + 2 * n_mels) = make_float4(r0.z, r1.z, r2.z, r3.z);
-          if (4 * f4 + 3 < rows) *reinterpret_cast<float4*>(dst + 3 * n_mels) = make_float4(r0.w, r1.w, r2.w, r3.w);
+          const bool v0 = 4 * f4 + 0 < rows, v1 = 4 * f4 + 1 < rows, v2 = 4 * f4 + 2 < rows, v3 = 4 * f4 + 3 < rows;
+          const float4 o0 = make_float4(finish(r0.x, v0), finish(r1.x, v0), finish(r2.x, v0), finish(r3.x, v0));
+          const float4 o1 = make_float4(finish(r0.y, v1), finish(r1.y, v1), finish(r2.y, v1), finish(r3.y, v1));
+          const float4 o2 = make_float4(finish(r0.z, v2), finish(r1.z, v2), finish(r2.z, v2), finish(r3.z, v2));
+          const float4 o3 = make_float4(finish(r0.w, v3), finish(r1.w, v3), finish(r2.w, v3), finish(r3.w, v3));
+          if (v0) *reinterpret_cast<float4*>(dst) = o0;
+          if (v1) *reinterpret_cast<float4*>(dst + n_mels) = o1;
+          if (v2) *reinterpret_cast<float4*>(dst + 2 * n_mels) = o2;
+          if (v3) *reinterpret_cast<float4*>(dst + 3 * n_mels) = o3;
         }
       } else {
         for (int f = warp; f < rows; f += kWarps)
-          for (int m = lane; m < n_mels; m += 32) out_tile[f * n_mels + m] = otile[m * kFramesPerCta + f];
+          for (int m = lane; m < n_mels; m += 32) out_tile[f * n_mels + m] = finish(otile[m * kFramesPerCta + f], true);
+      }
+      if (kNorm != YOHO_NORM_NONE) {
+        // per-warp partials now, the cross-warp sum after the next barrier (top of the loop / after it): fixed order, no atomics
+        const float a = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sum) : warp_max(acc_max);
+        const float b = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sq) : 0.0f;
+        if (lane == 0) { sm.red[warp] = a; sm.red[32 + warp] = b; }
+        pending_stats = clip * tiles_per_clip + tile;
       }
     }
-    if (kNorm != YOHO_NORM_NONE && warp == 0) {
-      float a, b;
-      if (kNorm == YOHO_NORM_REFERENCE) {
-        a = warp_sum(lane < kWarps ? sm.red[lane] : 0.0f);
-        b = warp_sum(lane < kWarps ? sm.red[32 + lane] : 0.0f);
-      } else {
-        a = warp_max(lane < kWarps ? sm.red[lane] : -INFINITY);
-        b = 0.0f;
-      }
-      if (lane == 0) stats[size_t(clip) * tiles_per_clip + tile] = make_float2(a, b);
-    }
+  }
+  if (kNorm != YOHO_NORM_NONE) {
+    __syncthreads();
+    write_stats();
   }
 }
 
@@ -671,7 +697,7 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
       const long long items = (long long)nb * tiles;
       const int grid = int(items < 2LL * ctx->num_sms ? items : 2LL * ctx->num_sms);
       kernel<<<grid, kThreads, sizeof(FrontendSmem<T>), stream>>>(
-          pcm, n_samples, total_samples, frames, c0, int(items), fb->d_bands, fb->d_weights, fb->n_pairs, fb->n_weights,
+          pcm, n_samples, total_samples, frames, c0, int(items), fb->d_bands, fb->d_weights, fb->n_groups, fb->n_weights,
           fb->n_mels, out, stats, tiles, vec_ok, vec_out);
       YOHO_LAUNCH_CHECK("logmel_kernel");
     }
