@@ -110,6 +110,18 @@ int yoho_logmel_s16(yoho_ctx* ctx, const yoho_filterbank* fb, const int16_t* pcm
                     int n_samples, int n_fft, int hop, float* out, int norm, void* ws,
                     size_t ws_bytes, yoho_stream_t stream);
 
+/* No counterpart in the reference.  Same computation as yoho_logmel_f32 for
+ * callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the per-tile
+ * statistics scratch lives in a file-scope device array of the library (256 KB, held by every GPU that loads the
+ * library until the process exits) instead of a caller-provided workspace, and the call performs no cudaMalloc / cudaFree
+ * or any other allocation.  Limit: batch * ceil(frames / 32) <= yoho_logmel_static_max_tiles() = 32768 statistics slots
+ * (e.g. 348 clips of 30 s); larger calls return YOHO_ERR_WORKSPACE.  All calls on a device share the array, which keeps
+ * the last call's contents (nothing in it needs to start at zero): calls that overlap on the GPU (different streams) race;
+ * serialise them on one stream or use yoho_logmel_f32. */
+size_t yoho_logmel_static_max_tiles(void);
+int yoho_logmel_f32_static(yoho_ctx* ctx, const yoho_filterbank* fb, const float* pcm, int batch,
+                           int n_samples, int n_fft, int hop, float* out, int norm, yoho_stream_t stream);
+
 /* Long-recording ingest (the step before the path: whisper.py:249-253, dataloaders.py:125-128): `recording`
  * holds total_samples mono samples on the device; clip b is recording[b * clip_samples, (b + 1) * clip_samples),
  * the last clip zero padded (np.pad, whisper.py:253).  Writes yoho_chunk_count(total_samples, clip_samples) =

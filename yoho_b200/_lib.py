@@ -57,6 +57,8 @@ SIGNATURES = {
     "yoho_logmel_workspace_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "yoho_logmel_f32": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _sz, _p]),
     "yoho_logmel_s16": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p, _sz, _p]),
+    "yoho_logmel_static_max_tiles": (_sz, []),
+    "yoho_logmel_f32_static": (_i, [_p, _p, _p, _i, _i, _i, _i, _p, _i, _p]),
     "yoho_chunk_count": (_i, [C.c_longlong, _i]),
     "yoho_logmel_chunked_f32": (_i, [_p, _p, _p, C.c_longlong, _i, _i, _i, _p, _i, _p, _sz, _p]),
     "yoho_logmel_chunked_s16": (_i, [_p, _p, _p, C.c_longlong, _i, _i, _i, _p, _i, _p, _sz, _p]),

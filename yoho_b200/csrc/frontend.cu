@@ -39,6 +39,7 @@
 
 #include <cmath>
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 
 namespace yoho {
@@ -802,4 +803,57 @@ extern "C" int yoho_normalize_f32(yoho_ctx* ctx, const float* spec, int batch, i
     YOHO_LAUNCH_CHECK("normalize_apply_kernel");
   }
   return YOHO_OK;
+}
+
+// ---- no-allocation variant of the fused log-mel call ------------------------------------------------------------------
+// For callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the
+// per-tile statistics scratch that yoho_logmel_f32 takes as `ws` lives in a file-scope device array instead.  Every GPU
+// that loads the library holds these 256 KB until the process exits.  All calls on a device share the array and it
+// keeps the last call's contents; nothing in it has to start at zero (every (clip, tile) slot a call reads was written
+// by the same call's logmel_kernel earlier on the same stream), but two calls that overlap on the GPU (different
+// streams) race on it.
+namespace {
+
+constexpr int kStaticStatsSlots = 32768;                          // float2 per-tile partials: batch * ceil(frames / 32) <= 32768
+static __device__ __align__(256) float2 g_logmel_static_stats[kStaticStatsSlots];
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mutex;
+float2* g_static_ptr[kStaticMaxDevices] = {};                     // device address of the array, per device (host code must not use the symbol's name)
+
+// Device address of g_logmel_static_stats on `device`: looked up once per device, with that device current.
+int static_stats_address(int device, float2** out) {
+  if (device < 0 || device >= kStaticMaxDevices) return fail(YOHO_ERR_UNSUPPORTED, "yoho_logmel_f32_static: device %d (at most %d devices)", device, kStaticMaxDevices);
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (!g_static_ptr[device]) {
+    int prev = -1;
+    YOHO_CUDA_CHECK(cudaGetDevice(&prev));
+    if (prev != device) YOHO_CUDA_CHECK(cudaSetDevice(device));
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_logmel_static_stats);
+    if (prev != device) cudaSetDevice(prev);
+    if (e != cudaSuccess || !p) return fail(YOHO_ERR_CUDA, "yoho_logmel_f32_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+    g_static_ptr[device] = static_cast<float2*>(p);
+  }
+  *out = g_static_ptr[device];
+  return YOHO_OK;
+}
+
+}  // namespace
+
+extern "C" size_t yoho_logmel_static_max_tiles(void) { return size_t(kStaticStatsSlots); }
+
+extern "C" int yoho_logmel_f32_static(yoho_ctx* ctx, const yoho_filterbank* fb, const float* pcm, int batch, int n_samples,
+                                      int n_fft, int hop, float* out, int norm, yoho_stream_t stream) {
+  if (!ctx) return fail(YOHO_ERR_INVALID, "yoho_logmel_f32_static: null context");
+  const int frames = frames_of(n_samples, n_fft, hop);
+  if (frames <= 0 || batch < 0) return fail(YOHO_ERR_INVALID, "yoho_logmel_f32_static: batch=%d n_samples=%d n_fft=%d hop=%d", batch, n_samples, n_fft, hop);
+  const long long slots = (long long)batch * logmel_tiles(frames);
+  if (slots > kStaticStatsSlots)
+    return fail(YOHO_ERR_WORKSPACE, "yoho_logmel_f32_static: %d clips x %d tiles = %lld statistics slots, the built-in scratch holds %d "
+                "(use yoho_logmel_f32 with a caller-provided workspace)", batch, logmel_tiles(frames), slots, kStaticStatsSlots);
+  float2* scratch = nullptr;
+  if (int rc = static_stats_address(ctx->device, &scratch)) return rc;
+  return logmel_launch<float>(ctx, fb, pcm, batch, n_samples, (long long)batch * n_samples, n_fft, hop, out, norm, scratch,
+                              size_t(kStaticStatsSlots) * sizeof(float2), static_cast<cudaStream_t>(stream));
 }
