@@ -77,7 +77,7 @@ int launch_layernorm_bf16(const float* x, const float* sc, const float* b, __nv_
 }
 
 // dst[n][k] = bf16(src[k][n]) through a 32x33 shared tile; columns k..ld_dst-1 are zeroed.
-__global__ void transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int k, int n, int ld_dst) {
+__global__ void transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int k, int n, int ld_dst, int k_pad) {
   __shared__ float tile[32][33];
   const int k0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
   for (int j = threadIdx.y; j < 32; j += blockDim.y) {
@@ -87,13 +87,14 @@ __global__ void transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat
   __syncthreads();
   for (int j = threadIdx.y; j < 32; j += blockDim.y) {
     int nn = n0 + j, kk = k0 + threadIdx.x;
-    if (nn < n && kk < ld_dst) dst[size_t(nn) * ld_dst + kk] = __float2bfloat16_rn(tile[threadIdx.x][j]);
+    if (nn < n && kk < k_pad) dst[size_t(nn) * ld_dst + kk] = __float2bfloat16_rn(tile[threadIdx.x][j]);
   }
 }
-int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, int ld_dst, cudaStream_t s) {
-  dim3 grid(ceil_div(n, 32), ceil_div(ld_dst, 32));
+int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, int ld_dst, cudaStream_t s, int k_pad) {
+  if (k_pad < 0) k_pad = ld_dst;
+  dim3 grid(ceil_div(n, 32), ceil_div(k_pad, 32));
   ProfScope prof(s, kProfOther, double(k) * n * 6.0);
-  transpose_cast_kernel<<<grid, dim3(32, 8), 0, s>>>(src, dst, k, n, ld_dst);
+  transpose_cast_kernel<<<grid, dim3(32, 8), 0, s>>>(src, dst, k, n, ld_dst, k_pad);
   YOHO_LAUNCH_CHECK("transpose_cast_kernel");
   return YOHO_OK;
 }
@@ -101,6 +102,11 @@ int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, in
 __global__ void cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n) {
   size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
   const size_t step = size_t(gridDim.x) * blockDim.x;
+  if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+    const size_t n4 = n >> 2;                                 // 128-bit loads, 64-bit stores
+    for (size_t v = i; v < n4; v += step) store4(dst + 4 * v, reinterpret_cast<const float4*>(src)[v]);
+    i += n4 << 2;
+  }
   for (; i < n; i += step) dst[i] = __float2bfloat16_rn(src[i]);
 }
 __global__ void cast_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, size_t n) {

@@ -13,7 +13,10 @@ namespace yoho {
 constexpr int kTensorsFixed = 7, kTensorsPerLayer = 15;
 
 static int conv_out_len(int frames) { return (frames + 2 - 3) / 2 + 1; }
-static int conv0_k(int n_mels) { return int(align_up(size_t(3 * n_mels), 64)); }
+// Conv_0 as three taps over the bf16 mel (B, F, M): every tap's K is rounded up to the 64-wide k-block; the columns
+// past M come out of the TMA as zeros (out of bounds), the matching weight columns are zero
+static int conv0_tap_k(int n_mels) { return int(align_up(size_t(n_mels), 64)); }
+static int conv0_k(int n_mels) { return 3 * conv0_tap_k(n_mels); }
 
 // Offsets (in bytes) of everything inside the packed weight blob.
 struct LayerOff {
@@ -86,6 +89,7 @@ static int check_desc(const yoho_enc_desc* d, const char* who) {
   if (d->dims != d->n_heads * 64)
     return fail(YOHO_ERR_UNSUPPORTED, "%s: dims=%d, n_heads=%d: kernels need d_head = 64 (every Whisper size)", who, d->dims, d->n_heads);
   if (d->dims > 1280) return fail(YOHO_ERR_UNSUPPORTED, "%s: dims=%d > 1280", who, d->dims);
+  if (d->n_mels % 8 != 0) return fail(YOHO_ERR_UNSUPPORTED, "%s: n_mels=%d must be a multiple of 8 (16-byte rows for the TMA of the conv stem)", who, d->n_mels);
   return YOHO_OK;
 }
 
@@ -109,7 +113,7 @@ static WsPlan plan_ws(const yoho_enc_desc& d, int batch, int frames, int compute
     w.qkv = take(B * T * 3 * D * e);
     w.att = take(B * T * D * e);
     const size_t h_bytes = B * T * 4 * D * e;
-    const size_t a0_bytes = B * Fp * conv0_k(d.n_mels) * e, c1_bytes = B * Fp * D * e;
+    const size_t a0_bytes = B * size_t(frames) * d.n_mels * e, c1_bytes = B * Fp * D * e;   // a0: bf16 copy of the mel
     const size_t stem = align_up(a0_bytes, 1024) + c1_bytes;
     w.h = take(h_bytes > stem ? h_bytes : stem);  // stem buffers are dead before the first Dense_0
     w.a0 = w.h;
@@ -141,7 +145,7 @@ static WsPlan plan_ws(const yoho_enc_desc& d, int batch, int frames, int compute
 static int forward_bf16(yoho_ctx* ctx, const yoho_enc_desc& d, const BlobLayout& L, const char* blob, const float* mel,
                         int batch, int frames, void* out, int out_dtype, char* ws, const WsPlan& w, cudaStream_t s) {
   using bf = __nv_bfloat16;
-  const int T = conv_out_len(frames), D = d.dims, Fp = 2 * T, K0 = conv0_k(d.n_mels);
+  const int T = conv_out_len(frames), D = d.dims, Fp = 2 * T, Kt = conv0_tap_k(d.n_mels);
   const int rows = batch * T;
   auto F32 = [&](size_t off) { return reinterpret_cast<const float*>(blob + off); };
   auto H16 = [&](size_t off) { return reinterpret_cast<const bf*>(blob + off); };
@@ -153,12 +157,15 @@ static int forward_bf16(yoho_ctx* ctx, const yoho_enc_desc& d, const BlobLayout&
   bf* att = reinterpret_cast<bf*>(ws + w.att);
   bf* hbuf = reinterpret_cast<bf*>(ws + w.h);
 
-  // Conv_0 + GELU (whisper.py:125-126): im2col'd rows x (D, K0) weights; rows >= frames stay zero
-  YOHO_TRY(launch_mel_im2col(mel, a0, batch, frames, Fp, d.n_mels, K0, s));
+  // Conv_0 + GELU (whisper.py:125-126) as an implicit GEMM: three shifted TMA boxes x[t-1], x[t], x[t+1] over the bf16 mel
+  // (B, F, M); padding=1 is the TMA's out-of-bounds zero fill (row -1 and row F of each clip), as is the K padding of each
+  // tap (columns M..Kt-1).  Output rows F..Fp-1 (the pad row Conv_1 reads) are stored as zeros.
+  YOHO_TRY(launch_cast_bf16(mel, a0, size_t(batch) * frames * d.n_mels, s));
   {
     GemmBf16Args g;
-    g.a = a0; g.a_ld = K0; g.a_cols = K0; g.batch = 1; g.rows_per_batch = batch * Fp;
-    g.w = H16(L.conv0_w_h); g.n = D; g.k_per_tap = K0; g.n_taps = 1;
+    g.a = a0; g.a_ld = d.n_mels; g.a_cols = d.n_mels; g.batch = batch; g.rows_per_batch = Fp; g.a_rows = frames;
+    g.w = H16(L.conv0_w_h); g.n = D; g.k_per_tap = Kt; g.n_taps = 3;
+    g.taps[0] = {0, -1}; g.taps[1] = {0, 0}; g.taps[2] = {0, 1};
     g.out_bf16 = c1; g.ldc = D; g.bias = F32(L.conv0_b); g.gelu = 1;
     g.mask_period = Fp; g.mask_valid = frames;
     YOHO_TRY(launch_gemm_bf16(ctx, g, s));
@@ -337,7 +344,9 @@ extern "C" int yoho_encoder_weights_pack(yoho_ctx* ctx, const yoho_enc_desc* des
   auto F32 = [&](size_t off) { return reinterpret_cast<const float*>(blob + off); };
   auto H16 = [&](size_t off) { return reinterpret_cast<bf*>(blob + off); };
   // Flax kernels are (in, out) / (k, in, out); the tensor-core path wants (out, in) with `in` contiguous.
-  YOHO_TRY(launch_transpose_cast(F32(L.conv0_w), H16(L.conv0_w_h), 3 * d.n_mels, D, conv0_k(d.n_mels), s));
+  for (int tap = 0; tap < 3; ++tap)   // (D, 3 * Kt): tap-major, each tap's n_mels columns followed by zeros up to Kt
+    YOHO_TRY(launch_transpose_cast(F32(L.conv0_w) + size_t(tap) * d.n_mels * D, H16(L.conv0_w_h) + size_t(tap) * conv0_tap_k(d.n_mels),
+                                   d.n_mels, D, conv0_k(d.n_mels), s, conv0_tap_k(d.n_mels)));
   YOHO_TRY(launch_transpose_cast(F32(L.conv1_w), H16(L.conv1_w_h), 3 * D, D, 3 * D, s));
   for (int i = 0; i < d.n_layers; ++i) {
     const LayerOff& l = L.layers[i];

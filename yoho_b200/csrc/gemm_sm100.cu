@@ -354,8 +354,9 @@ static int launch_gemm_bn(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s) 
   p.mask_period = a.mask_period; p.mask_valid = a.mask_valid;
 
   CUtensorMap map_a, map_w, map_c;
-  int r = make_tmap_bf16_3d(ctx->encode_tiled, &map_a, a.a, uint64_t(a.a_cols), uint64_t(a.rows_per_batch), uint64_t(a.batch),
-                            uint64_t(a.a_ld), uint64_t(a.a_ld) * uint64_t(a.rows_per_batch), kBlockK, kBlockM, 1);
+  const int a_rows = a.a_rows > 0 ? a.a_rows : a.rows_per_batch;      // rows past a_rows (and past either end of a clip, for the taps) read as zero
+  int r = make_tmap_bf16_3d(ctx->encode_tiled, &map_a, a.a, uint64_t(a.a_cols), uint64_t(a_rows), uint64_t(a.batch),
+                            uint64_t(a.a_ld), uint64_t(a.a_ld) * uint64_t(a_rows), kBlockK, kBlockM, 1);
   if (r) return fail(YOHO_ERR_CUDA, "gemm: cuTensorMapEncodeTiled(A) failed with CUresult %d (cols=%d rows=%d batch=%d ld=%d)", r, a.a_cols, a.rows_per_batch, a.batch, a.a_ld);
   const uint64_t k_total = uint64_t(a.n_taps) * uint64_t(a.k_per_tap);
   r = make_tmap_bf16_3d(ctx->encode_tiled, &map_w, a.w, k_total, uint64_t(a.n), 1, k_total, k_total * uint64_t(a.n), kBlockK, BN / 2, 1);
@@ -382,6 +383,7 @@ int launch_gemm_bf16(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s) {
   if (a.batch <= 0 || a.rows_per_batch <= 0) return YOHO_OK;
   if (a.n <= 0 || a.n % 32 != 0) return fail(YOHO_ERR_UNSUPPORTED, "gemm: n=%d must be a positive multiple of 32", a.n);
   if (a.n_taps < 1 || a.n_taps > 3) return fail(YOHO_ERR_INVALID, "gemm: n_taps=%d", a.n_taps);
+  if (a.a_rows < 0 || a.a_rows > a.rows_per_batch) return fail(YOHO_ERR_INVALID, "gemm: a_rows=%d of %d", a.a_rows, a.rows_per_batch);
   if (a.k_per_tap <= 0 || a.k_per_tap % 8 != 0 || (a.n_taps > 1 && a.k_per_tap % kBlockK != 0))
     return fail(YOHO_ERR_UNSUPPORTED, "gemm: k_per_tap=%d (multiple of 8; multiple of 64 with taps)", a.k_per_tap);
   if (a.a_ld % 8 != 0 || a.ldc % 8 != 0) return fail(YOHO_ERR_UNSUPPORTED, "gemm: leading dimensions must be multiples of 8 (a_ld=%d ldc=%d)", a.a_ld, a.ldc);

@@ -9,7 +9,7 @@ namespace yoho {
 int launch_layernorm_f32(const float* x, const float* scale, const float* bias, float* y, int rows, int dims, cudaStream_t s);
 int launch_layernorm_bf16(const float* x, const float* scale, const float* bias, __nv_bfloat16* y, int rows, int dims, cudaStream_t s);
 // dst (n, k) bf16 = transpose of src (k, n) float32; dst row stride ld_dst (>= k), tail zero-filled.
-int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, int ld_dst, cudaStream_t s);
+int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, int ld_dst, cudaStream_t s, int k_pad = -1);   // k_pad >= 0: zero only columns k..k_pad-1
 int launch_cast_bf16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t s);
 int launch_cast_f32(const __nv_bfloat16* src, float* dst, size_t n, cudaStream_t s);
 // mel (B, F, M) float32 -> (B, Fp, K0) bf16 rows [x[t-1], x[t], x[t+1], 0...]; rows t >= F are zero.
@@ -89,6 +89,7 @@ struct GemmBf16Args {
   // A: bf16, viewed as (batch, rows_per_batch, a_cols) row-major, row stride a_ld elements
   const __nv_bfloat16* a = nullptr; int a_ld = 0; int a_cols = 0;
   int batch = 1; int rows_per_batch = 0;
+  int a_rows = 0;                  // rows of A that exist per batch entry (0: rows_per_batch); rows beyond are TMA zero fill
   // W: bf16 (n, k_total) row-major ("K-major"), k_total = n_taps * k_per_tap (zero padded to 64)
   const __nv_bfloat16* w = nullptr; int n = 0; int k_per_tap = 0; int n_taps = 1;
   TapSpec taps[3] = {{0, 0}, {0, 0}, {0, 0}};
