@@ -164,7 +164,7 @@ static int forward_bf16(yoho_ctx* ctx, const yoho_enc_desc& d, const BlobLayout&
   {
     GemmBf16Args g;
     g.a = a0; g.a_ld = d.n_mels; g.a_cols = d.n_mels; g.batch = batch; g.rows_per_batch = Fp; g.a_rows = frames;
-    g.w = H16(L.conv0_w_h); g.n = D; g.k_per_tap = Kt; g.n_taps = 3;
+    g.w = H16(L.conv0_w_h); g.n = D; g.k_per_tap = Kt; g.n_taps = 3; g.flop_k = 3 * d.n_mels;
     g.taps[0] = {0, -1}; g.taps[1] = {0, 0}; g.taps[2] = {0, 1};
     g.out_bf16 = c1; g.ldc = D; g.bias = F32(L.conv0_b); g.gelu = 1;
     g.mask_period = Fp; g.mask_valid = frames;

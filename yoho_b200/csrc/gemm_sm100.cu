@@ -372,7 +372,7 @@ static int launch_gemm_bn(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s) 
   YOHO_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   const int max_clusters = ctx->num_sms / 2;
   const int clusters = p.total_tiles < max_clusters ? p.total_tiles : max_clusters;
-  ProfScope prof(s, kProfGemm, 2.0 * double(a.batch) * double(a.rows_per_batch) * double(a.n) * double(a.n_taps) * double(a.k_per_tap));
+  ProfScope prof(s, kProfGemm, 2.0 * double(a.batch) * double(a.rows_per_batch) * double(a.n) * double(a.flop_k > 0 ? a.flop_k : a.n_taps * a.k_per_tap));
   gemm_bf16_kernel<BN><<<2 * clusters, kGemmThreads, Cfg::kSmemBytes, s>>>(map_a, map_w, map_c, p);
   YOHO_LAUNCH_CHECK("gemm_bf16_kernel");
   return YOHO_OK;

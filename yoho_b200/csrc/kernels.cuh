@@ -89,6 +89,7 @@ struct GemmBf16Args {
   // A: bf16, viewed as (batch, rows_per_batch, a_cols) row-major, row stride a_ld elements
   const __nv_bfloat16* a = nullptr; int a_ld = 0; int a_cols = 0;
   int batch = 1; int rows_per_batch = 0;
+  int flop_k = 0;                  // contraction length the profiler counts as algorithmic work (0: n_taps * k_per_tap); Conv_0 pads each tap's K
   int a_rows = 0;                  // rows of A that exist per batch entry (0: rows_per_batch); rows beyond are TMA zero fill
   // W: bf16 (n, k_total) row-major ("K-major"), k_total = n_taps * k_per_tap (zero padded to 64)
   const __nv_bfloat16* w = nullptr; int n = 0; int k_per_tap = 0; int n_taps = 1;
