@@ -99,6 +99,35 @@ int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, in
   return YOHO_OK;
 }
 
+// LayerNorm folded into the GEMM that consumes it (GemmBf16Args::ln_*): one thread per output column n.
+//   w'[k] = scale[k] * src[k][n];  dst[n][k] = bf16(w'[k] - mean_k w');  bias_out[n] = bias_in[n] + sum_k beta[k] * src[k][n]
+__global__ void __launch_bounds__(128)
+ln_fold_kernel(const float* __restrict__ src, const float* __restrict__ scale, const float* __restrict__ beta,
+               const float* __restrict__ bias_in, __nv_bfloat16* __restrict__ dst, float* __restrict__ bias_out, int k, int n) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= n) return;
+  float c = 0.0f, b = bias_in ? bias_in[col] : 0.0f;
+  for (int kk = 0; kk < k; ++kk) {
+    const float w = src[size_t(kk) * n + col];
+    c = fmaf(scale[kk], w, c);
+    b = fmaf(beta[kk], w, b);
+  }
+  const float m = c / float(k);
+  __nv_bfloat16* row = dst + size_t(col) * k;
+  for (int kk = 0; kk < k; kk += 2) {                       // k is even (a multiple of 64 in every model)
+    const float w0 = src[size_t(kk) * n + col], w1 = src[size_t(kk + 1) * n + col];
+    *reinterpret_cast<__nv_bfloat162*>(row + kk) = __floats2bfloat162_rn(fmaf(scale[kk], w0, -m), fmaf(scale[kk + 1], w1, -m));
+  }
+  bias_out[col] = b;
+}
+int launch_ln_fold(const float* src, const float* scale, const float* beta, const float* bias_in, __nv_bfloat16* dst,
+                   float* bias_out, int k, int n, cudaStream_t s) {
+  if (k % 2 != 0) return fail(YOHO_ERR_UNSUPPORTED, "ln_fold: k=%d must be even", k);
+  ln_fold_kernel<<<ceil_div(n, 128), 128, 0, s>>>(src, scale, beta, bias_in, dst, bias_out, k, n);
+  YOHO_LAUNCH_CHECK("ln_fold_kernel");
+  return YOHO_OK;
+}
+
 __global__ void cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n) {
   size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
   const size_t step = size_t(gridDim.x) * blockDim.x;

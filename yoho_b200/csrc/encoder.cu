@@ -6,9 +6,17 @@
 //   YOHO_COMPUTE_FP32: SIMT fp32 kernels, the 1e-4 parity path.
 #include "kernels.cuh"
 
+#include <cstdlib>
 #include <vector>
 
 namespace yoho {
+
+// LayerNorm_0 / LayerNorm_1 of the blocks folded into the GEMMs around them (default) or run as stand-alone kernels
+// (YOHO_LN_FUSE=0: A/B measurement; read once per process, it decides what yoho_encoder_weights_pack writes)
+static bool ln_fuse() {
+  static const bool on = [] { const char* e = getenv("YOHO_LN_FUSE"); return !(e && e[0] == '0'); }();
+  return on;
+}
 
 constexpr int kTensorsFixed = 7, kTensorsPerLayer = 15;
 
@@ -22,7 +30,8 @@ static int conv0_k(int n_mels) { return 3 * conv0_tap_k(n_mels); }
 struct LayerOff {
   size_t ln0_s, ln0_b, wq, bq, wk, wv, bv, wo, bo, ln1_s, ln1_b, w1, b1, w2, b2;  // float32 originals
   size_t bqkv;                                                                   // float32 [bq | 0 | bv]
-  size_t wqkv_h, wo_h, w1_h, w2_h;                                               // bf16 (out, in)
+  size_t bqkv_ln, b1_ln;                                                         // float32: LayerNorm bias carried through the weights, beta @ W + bias
+  size_t wqkv_h, wo_h, w1_h, w2_h;                                               // bf16 (out, in); fused: wqkv_h / w1_h carry the LN scale, column means removed
 };
 struct BlobLayout {
   size_t conv0_w, conv0_b, conv1_w, conv1_b, pos, lnf_s, lnf_b;
@@ -73,6 +82,8 @@ static BlobLayout plan_blob(const yoho_enc_desc& d) {
   L.conv1_w_h = take(D * 3 * D * h);
   for (auto& l : L.layers) {
     l.bqkv = take(3 * D * f);
+    l.bqkv_ln = take(3 * D * f);
+    l.b1_ln = take(4 * D * f);
     l.wqkv_h = take(3 * D * D * h);
     l.wo_h = take(D * D * h);
     l.w1_h = take(4 * D * D * h);
@@ -96,7 +107,7 @@ static int check_desc(const yoho_enc_desc* d, const char* who) {
 // ------------------------------------------------------------------------------ workspace plan
 struct WsPlan {
   // bf16 path
-  size_t a0 = 0, c1 = 0, x = 0, xn = 0, qkv = 0, att = 0, h = 0, scores = 0;
+  size_t a0 = 0, c1 = 0, x = 0, xn = 0, qkv = 0, att = 0, h = 0, scores = 0, lnst = 0;
   int score_clips = 0;
   size_t total = 0;
 };
@@ -118,6 +129,7 @@ static WsPlan plan_ws(const yoho_enc_desc& d, int batch, int frames, int compute
     w.h = take(h_bytes > stem ? h_bytes : stem);  // stem buffers are dead before the first Dense_0
     w.a0 = w.h;
     w.c1 = w.h + align_up(a0_bytes, 1024);
+    w.lnst = take(B * T * size_t(gemm_ln_parts(d.dims)) * sizeof(float2));   // per-row {sum, sum of squares} partials of the residual stream
   } else {
     const size_t e = sizeof(float);
     w.x = take(B * T * D * e);
@@ -156,6 +168,8 @@ static int forward_bf16(yoho_ctx* ctx, const yoho_enc_desc& d, const BlobLayout&
   bf* qkv = reinterpret_cast<bf*>(ws + w.qkv);
   bf* att = reinterpret_cast<bf*>(ws + w.att);
   bf* hbuf = reinterpret_cast<bf*>(ws + w.h);
+  float2* lnst = reinterpret_cast<float2*>(ws + w.lnst);
+  const bool fuse = ln_fuse();
 
   // Conv_0 + GELU (whisper.py:125-126) as an implicit GEMM: three shifted TMA boxes x[t-1], x[t], x[t+1] over the bf16 mel
   // (B, F, M); padding=1 is the TMA's out-of-bounds zero fill (row -1 and row F of each clip), as is the K padding of each
@@ -180,9 +194,51 @@ static int forward_bf16(yoho_ctx* ctx, const yoho_enc_desc& d, const BlobLayout&
     g.taps[2] = {D, 0};   // x[2t+1] (row 2T-1 >= frames is the zeroed pad row)
     g.out_f32 = x; g.ldc = D; g.bias = F32(L.conv1_b); g.gelu = 1;
     g.pos = F32(L.pos); g.pos_period = T;
+    if (fuse && d.n_layers > 0) { g.xb_out = xn; g.xb_ld = D; g.ln_stats_out = lnst; }   // feeds LayerNorm_0 of the first block
     YOHO_TRY(launch_gemm_bf16(ctx, g, s));
   }
-  for (int i = 0; i < d.n_layers; ++i) {
+  // Fused: the LayerNorms of the blocks (whisper.py:77,82) have no kernel of their own.  Every GEMM that writes the residual
+  // stream x (float32) also writes xn = bf16(x) and per-row {sum, sum of squares} partials; the GEMM that consumes LN(x)
+  // runs on xn with weights that carry the LN scale (column means removed) and finishes the normalisation in its epilogue.
+  const int parts = gemm_ln_parts(D);
+  for (int i = 0; fuse && i < d.n_layers; ++i) {
+    const LayerOff& l = L.layers[i];
+    {   // q | k | v of LN(x)                         whisper.py:76-78, 43-46
+      GemmBf16Args g;
+      g.a = xn; g.a_ld = D; g.a_cols = D; g.batch = 1; g.rows_per_batch = rows;
+      g.w = H16(l.wqkv_h); g.n = 3 * D; g.k_per_tap = D;
+      g.out_bf16 = qkv; g.ldc = 3 * D; g.bias = F32(l.bqkv_ln);
+      g.ln_stats_in = lnst; g.ln_parts_in = parts; g.ln_dims = D;
+      YOHO_TRY(launch_gemm_bf16(ctx, g, s));
+    }
+    YOHO_TRY(launch_attention_bf16(ctx, qkv, att, batch, T, d.n_heads, s));
+    {   // x += out_proj(attention), and the inputs of LayerNorm_1     whisper.py:50, 79
+      GemmBf16Args g;
+      g.a = att; g.a_ld = D; g.a_cols = D; g.batch = 1; g.rows_per_batch = rows;
+      g.w = H16(l.wo_h); g.n = D; g.k_per_tap = D;
+      g.out_f32 = x; g.ldc = D; g.bias = F32(l.bo);
+      g.add_resid = 1; g.xb_out = xn; g.xb_ld = D; g.ln_stats_out = lnst;
+      YOHO_TRY(launch_gemm_bf16(ctx, g, s));
+    }
+    {   // gelu(Dense_0(LN(x)))                       whisper.py:82-84
+      GemmBf16Args g;
+      g.a = xn; g.a_ld = D; g.a_cols = D; g.batch = 1; g.rows_per_batch = rows;
+      g.w = H16(l.w1_h); g.n = 4 * D; g.k_per_tap = D;
+      g.out_bf16 = hbuf; g.ldc = 4 * D; g.bias = F32(l.b1_ln); g.gelu = 1;
+      g.ln_stats_in = lnst; g.ln_parts_in = parts; g.ln_dims = D;
+      YOHO_TRY(launch_gemm_bf16(ctx, g, s));
+    }
+    {   // x += Dense_1(...)                          whisper.py:85-86
+      GemmBf16Args g;
+      g.a = hbuf; g.a_ld = 4 * D; g.a_cols = 4 * D; g.batch = 1; g.rows_per_batch = rows;
+      g.w = H16(l.w2_h); g.n = D; g.k_per_tap = 4 * D;
+      g.out_f32 = x; g.ldc = D; g.bias = F32(l.b2);
+      if (i + 1 < d.n_layers) { g.add_resid = 1; g.xb_out = xn; g.xb_ld = D; g.ln_stats_out = lnst; }   // the next block's LayerNorm_0
+      else g.accumulate = 1;                                               // last block: the final LayerNorm reads x itself
+      YOHO_TRY(launch_gemm_bf16(ctx, g, s));
+    }
+  }
+  for (int i = 0; !fuse && i < d.n_layers; ++i) {
     const LayerOff& l = L.layers[i];
     // x += out_proj(attention(LN(x)))          whisper.py:76-79, 37-67
     YOHO_TRY(launch_layernorm_bf16(x, F32(l.ln0_s), F32(l.ln0_b), xn, rows, D, s));
@@ -350,16 +406,26 @@ extern "C" int yoho_encoder_weights_pack(yoho_ctx* ctx, const yoho_enc_desc* des
   YOHO_TRY(launch_transpose_cast(F32(L.conv1_w), H16(L.conv1_w_h), 3 * D, D, 3 * D, s));
   for (int i = 0; i < d.n_layers; ++i) {
     const LayerOff& l = L.layers[i];
-    YOHO_TRY(launch_transpose_cast(F32(l.wq), H16(l.wqkv_h), D, D, D, s));
-    YOHO_TRY(launch_transpose_cast(F32(l.wk), H16(l.wqkv_h) + size_t(D) * D, D, D, D, s));
-    YOHO_TRY(launch_transpose_cast(F32(l.wv), H16(l.wqkv_h) + size_t(2) * D * D, D, D, D, s));
-    YOHO_TRY(launch_transpose_cast(F32(l.wo), H16(l.wo_h), D, D, D, s));
-    YOHO_TRY(launch_transpose_cast(F32(l.w1), H16(l.w1_h), D, 4 * D, D, s));
-    YOHO_TRY(launch_transpose_cast(F32(l.w2), H16(l.w2_h), 4 * D, D, 4 * D, s));
     // fused bias [bq | 0 | bv]: key_proj has use_bias=False (whisper.py:33)
     YOHO_TRY(launch_fill_zero(blob + l.bqkv, size_t(3) * D * sizeof(float), s));
     YOHO_CUDA_CHECK(cudaMemcpyAsync(blob + l.bqkv, blob + l.bq, D * sizeof(float), cudaMemcpyDeviceToDevice, s));
     YOHO_CUDA_CHECK(cudaMemcpyAsync(blob + l.bqkv + size_t(2) * D * sizeof(float), blob + l.bv, D * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    if (ln_fuse()) {
+      // LayerNorm_0 / LayerNorm_1 (whisper.py:77,82) are folded into the GEMMs that consume them: the weights carry the LN
+      // scale and have their column means removed (the centring), the epilogue applies rstd, LN bias and Dense bias merge
+      auto Fp = [&](size_t off) { return reinterpret_cast<float*>(blob + off); };
+      YOHO_TRY(launch_ln_fold(F32(l.wq), F32(l.ln0_s), F32(l.ln0_b), F32(l.bqkv), H16(l.wqkv_h), Fp(l.bqkv_ln), D, D, s));
+      YOHO_TRY(launch_ln_fold(F32(l.wk), F32(l.ln0_s), F32(l.ln0_b), F32(l.bqkv) + D, H16(l.wqkv_h) + size_t(D) * D, Fp(l.bqkv_ln) + D, D, D, s));
+      YOHO_TRY(launch_ln_fold(F32(l.wv), F32(l.ln0_s), F32(l.ln0_b), F32(l.bqkv) + 2 * D, H16(l.wqkv_h) + size_t(2) * D * D, Fp(l.bqkv_ln) + 2 * D, D, D, s));
+      YOHO_TRY(launch_ln_fold(F32(l.w1), F32(l.ln1_s), F32(l.ln1_b), F32(l.b1), H16(l.w1_h), Fp(l.b1_ln), D, 4 * D, s));
+    } else {
+      YOHO_TRY(launch_transpose_cast(F32(l.wq), H16(l.wqkv_h), D, D, D, s));
+      YOHO_TRY(launch_transpose_cast(F32(l.wk), H16(l.wqkv_h) + size_t(D) * D, D, D, D, s));
+      YOHO_TRY(launch_transpose_cast(F32(l.wv), H16(l.wqkv_h) + size_t(2) * D * D, D, D, D, s));
+      YOHO_TRY(launch_transpose_cast(F32(l.w1), H16(l.w1_h), D, 4 * D, D, s));
+    }
+    YOHO_TRY(launch_transpose_cast(F32(l.wo), H16(l.wo_h), D, D, D, s));
+    YOHO_TRY(launch_transpose_cast(F32(l.w2), H16(l.w2_h), 4 * D, D, 4 * D, s));
   }
   return YOHO_OK;
 }

@@ -47,9 +47,19 @@ struct GemmParams {
   int pos_period;
   int accumulate;
   int mask_period, mask_valid;
+  // LayerNorm folding (kLn kernels only; see GemmBf16Args)
+  int add_resid;
+  __nv_bfloat16* xb_out; int xb_ld;
+  float2* ln_stats_out; int ln_parts_out;
+  const float2* ln_stats_in; int ln_parts_in; float ln_inv_dims;
 };
 
-template <int BN> struct GemmCfg {
+// kLn: 0 plain; 1 LayerNorm consumer (rows scaled by rstd from the partials); 2 LayerNorm producer (residual rows fetched by
+// TMA, bf16 copy, partials)
+// kDeep (producers with a short K, i.e. memory-bound ones): three staging buffers per epilogue warp keep two residual
+// loads in flight per warp (one is not enough: 8 warps x 4 KB per SM over ~1.2 us of DRAM latency caps at ~4 TB/s), paid
+// for with operand stages the short main loop does not need
+template <int BN, int kLn = 0, bool kDeep = false> struct GemmCfg {
   static constexpr int kABytes = kBlockM * kBlockK * 2;          // 16 KB
   static constexpr int kBBytes = (BN / 2) * kBlockK * 2;         // this CTA's half of the B tile
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -59,11 +69,15 @@ template <int BN> struct GemmCfg {
 #ifndef YOHO_GEMM_STAGES_256
 #define YOHO_GEMM_STAGES_256 6
 #endif
-  static constexpr int kStages = BN == 256 ? YOHO_GEMM_STAGES_256 : 6;
-  static constexpr int kEpiBufs = (BN == 256 && kStages > 5) ? 1 : 2;     // staging buffers per epilogue warp
+  // the producer's epilogue needs two staging buffers per warp (the next chunk's residual rows arrive while this chunk is
+  // finished): it runs on five operand stages
+  static constexpr int kStages = kDeep ? (BN == 256 ? 4 : 5) : (BN == 256 ? (kLn == 2 ? 5 : YOHO_GEMM_STAGES_256) : 6);
+  static constexpr int kEpiBufs = kDeep ? 3 : ((BN == 256 && kStages > 5) ? 1 : 2);     // staging buffers per epilogue warp
   static constexpr int kStagingBytes = kEpiWarps * kEpiBufs * kStageBufBytes;   // 32 or 64 KB
   static constexpr int kTmemCols = 2 * BN;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kBarrierBytes = 512;   // 2 * kStages + 4 pipeline barriers, the TMEM slot, 2 * kEpiWarps residual barriers
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + kBarrierBytes;
+  static_assert((2 * kStages + 4 + 1 + kEpiBufs * kEpiWarps) * 8 <= kBarrierBytes, "barrier area");
   static_assert(kSmemBytes <= 232448, "exceeds the 227 KB dynamic shared memory limit");
 };
 
@@ -96,8 +110,20 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 }
 
 // Epilogue math on 32 consecutive output columns [col0, col0+32) of this thread's row.
-__device__ __forceinline__ void epilogue_math(float (&v)[32], const GemmParams& p, int col0, const float* pos_row, bool masked) {
-  if (p.bias) {
+__device__ __forceinline__ void epilogue_math(float (&v)[32], const GemmParams& p, int col0, const float* pos_row, bool masked,
+                                              bool ln_scale = false, float ln_rstd = 1.0f) {
+  if (ln_scale) {
+    // LN(x) W + b = rstd * (x W'') + b': the GEMM ran on the raw rows and on weights that carry the LN scale and have their
+    // column means removed; b' = beta W + b.  One packed FMA per pair replaces the bias add.
+    const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
+    const uint64_t r2 = pack_f32x2(ln_rstd, ln_rstd);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float4 bv = __ldg(bp + j);
+      unpack_f32x2(fma_f32x2(pack_f32x2(v[4 * j], v[4 * j + 1]), r2, pack_f32x2(bv.x, bv.y)), v[4 * j], v[4 * j + 1]);
+      unpack_f32x2(fma_f32x2(pack_f32x2(v[4 * j + 2], v[4 * j + 3]), r2, pack_f32x2(bv.z, bv.w)), v[4 * j + 2], v[4 * j + 3]);
+    }
+  } else if (p.bias) {
     const float4* bp = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -123,11 +149,11 @@ __device__ __forceinline__ void epilogue_math(float (&v)[32], const GemmParams& 
   }
 }
 
-template <int BN>
+template <int BN, int kLn, bool kDeep>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_c, const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, kLn, kDeep>;
   extern __shared__ unsigned char smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   unsigned char* smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
@@ -138,6 +164,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint64_t* tmem_full = empty_bar + Cfg::kStages;
   uint64_t* tmem_empty = tmem_full + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* resid_bar = tmem_empty + 3;            // [epilogue warp][staging buffer]: the TMA of the old residual rows has landed
 
   // warp index through a shuffle: ptxas then treats it (and everything in the role branches that derives from it) as
   // warp-uniform, which keeps the producer's and the MMA issuer's loops on the uniform datapath
@@ -153,6 +180,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < Cfg::kStages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 2 * kEpiWarps); }
+    if (kLn == 2) for (int i = 0; i < Cfg::kEpiBufs * kEpiWarps; ++i) mbar_init(&resid_bar[i], 1);
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -228,6 +256,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     const int sw = lane & 7;
     int buf = 0;
     int it = 0;
+    uint64_t* my_rbar = resid_bar + (warp - 4) * Cfg::kEpiBufs;     // producer: one barrier per staging buffer
+    uint32_t rphase = 0;                               // bit b: parity the next wait on my_rbar[b] uses
+    // consumer: up to ten {sum, sum of squares} partials of this lane's row (dims <= 1280), two per load, fetched one tile
+    // ahead: the epilogue is the critical path of the GELU GEMM and must not wait for an L2 round trip per tile
+    float4 stat[5];
+    auto load_stats = [&](int t) {
+      const int bm2 = t / p.tiles_n, b2 = bm2 / p.tiles_m, mb2 = bm2 - b2 * p.tiles_m;
+      const int r = mb2 * kPairM + int(rank) * kBlockM + q * 32 + lane;
+      const bool ok = r < p.rows_per_batch;
+      const float4* st = reinterpret_cast<const float4*>(p.ln_stats_in + (size_t(b2) * size_t(p.rows_per_batch) + size_t(ok ? r : 0)) * size_t(p.ln_parts_in));
+#pragma unroll
+      for (int i = 0; i < 5; ++i) stat[i] = (ok && 2 * i < p.ln_parts_in) ? __ldg(st + i) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    };
+    if (kLn == 1 && cluster_id < p.total_tiles) load_stats(cluster_id);
     for (int tile = cluster_id; tile < p.total_tiles; tile += n_clusters, ++it) {
       const int as = it & 1; const uint32_t aphase = (it >> 1) & 1;
       const int nb = tile % p.tiles_n, bm = tile / p.tiles_n;
@@ -237,8 +279,43 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       const bool masked = p.mask_period > 0 && (r_in_batch % p.mask_period) >= p.mask_valid;
       const float* pos_row = p.pos ? p.pos + size_t(r_in_batch % p.pos_period) * p.n : nullptr;
       const bool warp_live = warp_row0 < p.rows_per_batch;     // warp-uniform: any row of this warp inside the batch
+      // ---- LayerNorm folding: whatever does not need the accumulator is fetched before the wait for it ----
+      const bool row_ok = r_in_batch < p.rows_per_batch;
+      const size_t grow = size_t(b) * size_t(p.rows_per_batch) + size_t(r_in_batch);     // row of the (rows, n) output
+      float ln_rstd = 1.0f;
+      const bool fetch = kLn == 2 && p.add_resid != 0;
+      // old residual rows of a 32-column chunk -> staging buffer sb (TMA, zero fill past the last row); the buffer's previous
+      // store must have left shared memory
+      auto issue_resid = [&](int sb, int col) {
+        if (lane == 0) {
+          tma_store_wait_read<Cfg::kEpiBufs - 2>();      // two buffers: the previous chunk's store; three: the one before it
+          mbar_arrive_expect_tx(&my_rbar[sb], kStageBufBytes);
+          tma_load_3d(my_stage + sb * kStageBufBytes, &map_c, &my_rbar[sb], col, warp_row0, b);
+        }
+      };
+      // chunks of this warp in this tile: columns nb * BN + (half + 2 j) * 32, j < nchunks; chunk j lives in staging buffer
+      // (buf + j) % kEpiBufs and its old rows are requested one chunk ahead.  With three buffers the buffer that is refilled
+      // belongs to the chunk before the previous one, so the request never waits for a store to drain.
+      constexpr int kAhead = 1;
+      int nchunks = 0;
+      if (kLn == 2 && fetch && warp_live) {
+        const int cols_left = p.n - nb * BN - half * 32;          // > 0: this warp's first chunk exists
+        nchunks = cols_left > 0 ? min((BN / 32 - half + 1) / 2, (cols_left + 63) / 64) : 0;
+#pragma unroll
+        for (int j = 0; j < kAhead; ++j)
+          if (j < nchunks) issue_resid((buf + j) % Cfg::kEpiBufs, nb * BN + (half + 2 * j) * 32);
+      }
+      int chunk_j = 0;
+      float st_sum = 0.0f, st_sq = 0.0f;
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
+      if (kLn == 1) {
+        const float ssum = ((stat[0].x + stat[0].z) + (stat[1].x + stat[1].z)) + ((stat[2].x + stat[2].z) + (stat[3].x + stat[3].z)) + (stat[4].x + stat[4].z);
+        const float ssq = ((stat[0].y + stat[0].w) + (stat[1].y + stat[1].w)) + ((stat[2].y + stat[2].w) + (stat[3].y + stat[3].w)) + (stat[4].y + stat[4].w);
+        const float mean = ssum * p.ln_inv_dims;
+        ln_rstd = rsqrtf(fmaxf(0.0f, ssq * p.ln_inv_dims - mean * mean) + 1e-6f);   // flax: var = E[x^2] - E[x]^2 >= 0, eps 1e-6
+        if (tile + n_clusters < p.total_tiles) load_stats(tile + n_clusters);
+      }
       const uint32_t t_addr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
       // The accumulator stage goes back to the MMA warp as soon as this warp's LAST chunk of it is in registers, not after
       // that chunk's math / staging / TMA store; the arrive carries no release fence (the payload is TMEM, ordered by the
@@ -258,17 +335,64 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           for (int c = half; c < BN / 32; c += 2) {
             const int col0 = nb * BN + c * 32;
             if (col0 >= p.n) break;  // warp-uniform
+            const bool last_chunk = c + 2 >= BN / 32 || col0 + 64 >= p.n;   // warp-uniform: no further chunk for this warp
             uint32_t acc[32];
             tmem_ld_32x32b_x32(t_addr + uint32_t(c * 32), acc);
+            unsigned char* sbuf = my_stage + buf * kStageBufBytes;
+            float4 bias4[8];                                                // fetched ahead of the waits below (producer: the chain per chunk is the critical path)
+            if (kLn == 2 && p.bias) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) bias4[j] = __ldg(reinterpret_cast<const float4*>(p.bias + col0) + j);
+            }
+            if (kLn == 2 && fetch) {
+              if (Cfg::kEpiBufs >= 3 && chunk_j + kAhead < nchunks) issue_resid((buf + kAhead) % Cfg::kEpiBufs, col0 + 64 * kAhead);
+              mbar_wait(&my_rbar[buf], (rphase >> buf) & 1u);             // this chunk's old rows (requested a chunk ago)
+              rphase ^= 1u << buf;
+            }
             tmem_ld_wait();
-            if (c + 2 >= BN / 32 || col0 + 64 >= p.n) release_acc();    // warp-uniform: no further chunk for this warp
+            if (last_chunk) release_acc();
             float v[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc[j]);
-            epilogue_math(v, p, col0, pos_row, masked);
-            unsigned char* sbuf = my_stage + buf * kStageBufBytes;
-            if (lane == 0) tma_store_wait_read<Cfg::kEpiBufs - 1>();     // the previous user of this buffer has been read out
-            __syncwarp();
+            if (kLn == 2 && p.bias && !p.gelu && !pos_row && !masked) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) { v[4 * j] += bias4[j].x; v[4 * j + 1] += bias4[j].y; v[4 * j + 2] += bias4[j].z; v[4 * j + 3] += bias4[j].w; }
+            } else {
+              epilogue_math(v, p, col0, pos_row, masked);
+            }
+            if (kLn == 2) {
+              if (fetch) {                                                  // x_new = x_old + value
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float4 xo = *reinterpret_cast<const float4*>(sbuf + lane * 128 + ((j ^ sw) << 4));
+                  v[4 * j] += xo.x; v[4 * j + 1] += xo.y; v[4 * j + 2] += xo.z; v[4 * j + 3] += xo.w;
+                }
+              }
+              if (p.ln_stats_out) {
+                float s0 = 0.0f, s1 = 0.0f, q0 = 0.0f, q1 = 0.0f;
+#pragma unroll
+                for (int j = 0; j < 32; j += 2) { s0 += v[j]; s1 += v[j + 1]; q0 = fmaf(v[j], v[j], q0); q1 = fmaf(v[j + 1], v[j + 1], q1); }
+                st_sum += s0 + s1;
+                st_sq += q0 + q1;
+              }
+              if (p.xb_out && row_ok) {                                     // bf16 copy of the new rows: 64 contiguous bytes per lane
+                uint4* xb = reinterpret_cast<uint4*>(p.xb_out + grow * size_t(p.xb_ld) + col0);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  xb[j] = make_uint4(pack_bf16(v[8 * j], v[8 * j + 1]), pack_bf16(v[8 * j + 2], v[8 * j + 3]),
+                                     pack_bf16(v[8 * j + 4], v[8 * j + 5]), pack_bf16(v[8 * j + 6], v[8 * j + 7]));
+              }
+            }
+            if (kLn == 2 && fetch) {
+              // request the rows of chunk j + kAhead: they go to the buffer of chunk j - 1, whose store was committed a whole
+              // chunk of arithmetic ago
+              if (Cfg::kEpiBufs < 3 && chunk_j + kAhead < nchunks) issue_resid((buf + kAhead) % Cfg::kEpiBufs, col0 + 64 * kAhead);
+              ++chunk_j;
+            }
+            if (!(kLn == 2 && fetch)) {                                     // (with fetch the landed load already proves the buffer free)
+              if (lane == 0) tma_store_wait_read<Cfg::kEpiBufs - 1>();     // the previous user of this buffer has been read out
+              __syncwarp();
+            }
 #pragma unroll
             for (int j = 0; j < 8; ++j)
               *reinterpret_cast<float4*>(sbuf + lane * 128 + ((j ^ sw) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
@@ -281,6 +405,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             }
             buf = (buf + 1) % Cfg::kEpiBufs;
           }
+          if (kLn == 2 && p.ln_stats_out && row_ok)                         // a warp without a chunk in this tile contributes zeros
+            p.ln_stats_out[grow * size_t(p.ln_parts_out) + size_t(nb * 2 + half)] = make_float2(st_sum, st_sq);
         } else {
           // 64 bf16 columns (= 128 B rows) per staging buffer
 #pragma unroll 1
@@ -299,7 +425,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
               float v[32];
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc0[j]);
-              epilogue_math(v, p, col0, pos_row, masked);
+              epilogue_math(v, p, col0, pos_row, masked, kLn == 1, ln_rstd);
 #pragma unroll
               for (int j = 0; j < 4; ++j)
                 *reinterpret_cast<uint4*>(sbuf + lane * 128 + ((j ^ sw) << 4)) =
@@ -310,7 +436,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
               float v[32];
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(acc1[j]);
-              epilogue_math(v, p, col0 + 32, pos_row, masked);
+              epilogue_math(v, p, col0 + 32, pos_row, masked, kLn == 1, ln_rstd);
 #pragma unroll
               for (int j = 0; j < 4; ++j)
                 *reinterpret_cast<uint4*>(sbuf + lane * 128 + (((4 + j) ^ sw) << 4)) =
@@ -337,9 +463,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   if (warp == 2) tmem_dealloc_2cta<Cfg::kTmemCols>(tmem_base);
 }
 
-template <int BN>
+static bool gemm_picks_bn256(int n) { return n % 256 == 0 || n > 1024; }
+int gemm_ln_parts(int n) { return 2 * ceil_div(n, gemm_picks_bn256(n) ? 256 : 128); }
+
+template <int BN, int kLn, bool kDeep = false>
 static int launch_gemm_bn(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, kLn, kDeep>;
   GemmParams p{};
   p.batch = a.batch; p.rows_per_batch = a.rows_per_batch; p.n = a.n;
   p.tiles_m = ceil_div(a.rows_per_batch, kPairM);
@@ -352,6 +481,9 @@ static int launch_gemm_bn(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s) 
   p.out_is_f32 = a.out_f32 != nullptr; p.bias = a.bias; p.gelu = a.gelu;
   p.pos = a.pos; p.pos_period = a.pos_period > 0 ? a.pos_period : 1; p.accumulate = a.accumulate;
   p.mask_period = a.mask_period; p.mask_valid = a.mask_valid;
+  p.add_resid = a.add_resid; p.xb_out = a.xb_out; p.xb_ld = a.xb_ld;
+  p.ln_stats_out = a.ln_stats_out; p.ln_parts_out = 2 * p.tiles_n;
+  p.ln_stats_in = a.ln_stats_in; p.ln_parts_in = a.ln_parts_in; p.ln_inv_dims = a.ln_dims > 0 ? 1.0f / float(a.ln_dims) : 0.0f;
 
   CUtensorMap map_a, map_w, map_c;
   const int a_rows = a.a_rows > 0 ? a.a_rows : a.rows_per_batch;      // rows past a_rows (and past either end of a clip, for the taps) read as zero
@@ -369,11 +501,11 @@ static int launch_gemm_bn(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s) 
                      uint64_t(a.ldc) * 2, uint64_t(a.ldc) * 2 * uint64_t(a.rows_per_batch), 64, 32, 1);
   if (r) return fail(YOHO_ERR_CUDA, "gemm: cuTensorMapEncodeTiled(C) failed with CUresult %d (n=%d rows=%d batch=%d ldc=%d)", r, a.n, a.rows_per_batch, a.batch, a.ldc);
 
-  YOHO_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  YOHO_CUDA_CHECK(cudaFuncSetAttribute(gemm_bf16_kernel<BN, kLn, kDeep>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
   const int max_clusters = ctx->num_sms / 2;
   const int clusters = p.total_tiles < max_clusters ? p.total_tiles : max_clusters;
   ProfScope prof(s, kProfGemm, 2.0 * double(a.batch) * double(a.rows_per_batch) * double(a.n) * double(a.flop_k > 0 ? a.flop_k : a.n_taps * a.k_per_tap));
-  gemm_bf16_kernel<BN><<<2 * clusters, kGemmThreads, Cfg::kSmemBytes, s>>>(map_a, map_w, map_c, p);
+  gemm_bf16_kernel<BN, kLn, kDeep><<<2 * clusters, kGemmThreads, Cfg::kSmemBytes, s>>>(map_a, map_w, map_c, p);
   YOHO_LAUNCH_CHECK("gemm_bf16_kernel");
   return YOHO_OK;
 }
@@ -391,7 +523,21 @@ int launch_gemm_bf16(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s) {
   const void* out = a.out_f32 ? static_cast<const void*>(a.out_f32) : static_cast<const void*>(a.out_bf16);
   if (reinterpret_cast<uintptr_t>(out) % 16 != 0) return fail(YOHO_ERR_INVALID, "gemm: output must be 16-byte aligned");
   if (a.accumulate && !a.out_f32) return fail(YOHO_ERR_INVALID, "gemm: accumulate needs a float32 output");
-  return (a.n % 256 == 0 || a.n > 1024) ? launch_gemm_bn<256>(ctx, a, s) : launch_gemm_bn<128>(ctx, a, s);
+  const bool producer = a.add_resid || a.xb_out || a.ln_stats_out, consumer = a.ln_stats_in != nullptr;
+  if (producer) {
+    if (consumer) return fail(YOHO_ERR_INVALID, "gemm: one GEMM is a LayerNorm producer or a consumer, not both");
+    if (!a.out_f32 || a.accumulate) return fail(YOHO_ERR_INVALID, "gemm: the LayerNorm producer outputs need a float32 output without TMA accumulation");
+    if (a.xb_out && (a.xb_ld % 8 != 0 || reinterpret_cast<uintptr_t>(a.xb_out) % 16 != 0)) return fail(YOHO_ERR_INVALID, "gemm: xb_out must be 16-byte aligned with a row stride that is a multiple of 8");
+    if (a.add_resid && a.n_taps * a.k_per_tap <= 1024)     // memory-bound: deep residual prefetch, fewer operand stages
+      return gemm_picks_bn256(a.n) ? launch_gemm_bn<256, 2, true>(ctx, a, s) : launch_gemm_bn<128, 2, true>(ctx, a, s);
+    return gemm_picks_bn256(a.n) ? launch_gemm_bn<256, 2>(ctx, a, s) : launch_gemm_bn<128, 2>(ctx, a, s);
+  }
+  if (consumer) {
+    if (!a.out_bf16 || !a.bias || a.ln_dims <= 0 || a.ln_parts_in <= 0)
+      return fail(YOHO_ERR_INVALID, "gemm: the LayerNorm consumer needs a bf16 output, the folded bias, ln_dims and ln_parts_in");
+    return gemm_picks_bn256(a.n) ? launch_gemm_bn<256, 1>(ctx, a, s) : launch_gemm_bn<128, 1>(ctx, a, s);
+  }
+  return gemm_picks_bn256(a.n) ? launch_gemm_bn<256, 0>(ctx, a, s) : launch_gemm_bn<128, 0>(ctx, a, s);
 }
 
 }  // namespace yoho

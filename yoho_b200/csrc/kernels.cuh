@@ -100,10 +100,28 @@ struct GemmBf16Args {
   int gelu = 0;
   const float* pos = nullptr;      // (rows_per_batch.., n): + pos[r % pos_period][col]
   int pos_period = 1;
-  int accumulate = 0;              // out_f32 += value (residual stream)
+  int accumulate = 0;              // out_f32 += value (residual stream), a TMA reduce-add performed in L2
   int mask_period = 0, mask_valid = 0;  // if mask_period: rows with (r % mask_period) >= mask_valid store 0
+  // ---- LayerNorm folded into the GEMMs on either side of it (whisper.py:77,82: x + f(LN(x))) -------------------------
+  // producer (float32 output = the residual stream x): with add_resid the epilogue fetches the old rows of out_f32 by TMA
+  // into its staging buffer, adds them and stores the new rows (instead of the reduce-add in L2, which never shows the
+  // sum to the SM); a bf16 copy of the new rows goes to xb_out (row stride xb_ld) and per-row partial {sum, sum of
+  // squares} over each epilogue warp's columns to ln_stats_out[row * gemm_ln_parts(n) + part]
+  int add_resid = 0;
+  __nv_bfloat16* xb_out = nullptr; int xb_ld = 0;
+  float2* ln_stats_out = nullptr;
+  // consumer: A holds the RAW rows x in bf16; W carries the LayerNorm scale and has its column means removed (the centring
+  // x - mean(x) is the projection I - 11^T/D, folded into the weights: (P x)^T W' = x^T (P W')), bias = beta W + b; the
+  // epilogue applies value = rstd * acc + bias[col] with rstd from the ln_parts_in partials of the row
+  const float2* ln_stats_in = nullptr; int ln_parts_in = 0; int ln_dims = 0;
 };
 int launch_gemm_bf16(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s);
+// partials per row that a producer GEMM with n output columns writes to ln_stats_out (two epilogue warps per column tile)
+int gemm_ln_parts(int n);
+// weight preparation for the consumer: with w'[k][n] = scale[k] * src[k][n] and m[n] = mean_k w'[k][n],
+// dst (n, k) bf16 = transpose of (w' - m);  bias_out[n] = (bias_in ? bias_in[n] : 0) + sum_k beta[k] * src[k][n]
+int launch_ln_fold(const float* src, const float* scale, const float* beta, const float* bias_in, __nv_bfloat16* dst,
+                   float* bias_out, int k, int n, cudaStream_t s);
 
 // ---------------------------------------------------------------- attention_sm100.cu (tcgen05)
 // qkv (batch, t, 3*dims) bf16 with q | k | v column blocks, heads of 64; out (batch, t, dims) bf16.
