@@ -71,6 +71,27 @@ for chunk in (32, 64, 128):
         for b0, n in even:
             enc.encoder(enc.logmel(pcm_dev[b0:b0 + n], enc._mel_buf(n)), out_dev[b0:b0 + n])
     print(f"device, even chunks of {chunk:3d}: {timed(device_even):8.2f} ms")
+# alternate chunks on two compute streams (own workspaces): the wave tails / launch bubbles of one chunk's kernels are
+# filled by the other chunk's kernels
+streams2 = [torch.cuda.Stream(), torch.cuda.Stream()]
+
+
+def device_two_streams(pl):
+    cur = torch.cuda.current_stream()
+    for st in streams2:
+        st.wait_stream(cur)
+    for i, (b0, n) in enumerate(pl):
+        with torch.cuda.stream(streams2[i & 1]):
+            mel = enc.logmel(pcm_dev[b0:b0 + n], enc._mel_buf(n, slot=10 + (i & 1)), ws_tag=f"logmel{i & 1}")
+            enc.encoder(mel, out_dev[b0:b0 + n], ws_tag=f"encoder{i & 1}")
+    for st in streams2:
+        cur.wait_stream(st)
+
+
+print(f"device, e2e plan, 2 streams:{timed(lambda: device_two_streams(plan)):8.2f} ms")
+for chunk in (32, 64):
+    even = [(b0, min(chunk, B - b0)) for b0 in range(0, B, chunk)]
+    print(f"device, even {chunk:3d}, 2 streams:{timed(lambda: device_two_streams(even)):8.2f} ms")
 print(f"e2e:                        {timed(lambda: enc.encode_host(pcm_host, out_host, chunk_clips=args.chunk)):8.2f} ms")
 
 # one direction stubbed out: the "host" buffer of that direction is a device tensor (the copy becomes a cheap D2D)

@@ -48,7 +48,7 @@ for chunk in (32, 64, 128):
     for taper in (True, False):
         ms = timed(lambda: enc.encode_host(pcm_host, out_host, chunk_clips=chunk, taper=taper))
         print(f"chunk {chunk:3d} taper {taper!s:5s}: {ms:7.2f} ms  plan {[n for _, n in orig_plan(B, min(chunk, (B + 1) // 2), taper)]}")
-for sizes in ([32, 96, 64, 32, 32], [32, 96, 64, 48, 16], [32, 96, 80, 32, 16], [24, 104, 64, 48, 16], [32, 96, 96, 32], [16, 112, 80, 32, 16], [32, 96, 64, 32, 32]):
+for sizes in ([16, 48, 64, 64, 32, 16, 16], [16, 48, 64, 64, 32, 16, 8, 8], [16, 32, 64, 64, 48, 16, 8, 8], [8, 24, 64, 64, 64, 16, 8, 8], [16, 48, 96, 64, 16, 8, 8], [32, 64, 64, 64, 16, 8, 8], [16, 48, 64, 64, 40, 12, 6, 6], [16, 16, 64, 64, 64, 16, 8, 8], [16, 48, 128, 32, 16, 8, 8]):
     if sum(sizes) != B:
         continue
     def plan(batch, chunk, taper=True, sizes=sizes):

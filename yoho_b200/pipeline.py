@@ -89,7 +89,7 @@ class ClipEncoder:
             self._mel[slot] = buf
         return buf[:batch]
 
-    def logmel(self, pcm: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    def logmel(self, pcm: torch.Tensor, out: torch.Tensor | None = None, ws_tag: str = "logmel") -> torch.Tensor:
         """(B, n_samples) float32/int16 CUDA tensor -> (B, frames, n_mels) float32, on the current stream."""
         rt, lib = self.rt, self.rt.lib
         B = pcm.shape[0]
@@ -98,7 +98,7 @@ class ClipEncoder:
         if out is None:
             out = torch.empty((B, self.frames, self.n_mels), dtype=torch.float32, device=rt.device)
         ws_bytes = lib.yoho_logmel_workspace_bytes(B, self.n_samples, self.n_fft, self.hop, self.n_mels)
-        ws = rt.workspace("logmel", ws_bytes)
+        ws = rt.workspace(ws_tag, ws_bytes)
         fn = lib.yoho_logmel_s16 if pcm.dtype == torch.int16 else lib.yoho_logmel_f32
         check(fn(rt.ctx, self.fb, C.c_void_p(pcm.data_ptr()), B, self.n_samples, self.n_fft, self.hop,
                  C.c_void_p(out.data_ptr()), self.norm, C.c_void_p(rt.aligned_ptr(ws)), ws_bytes, rt.stream_ptr()))
@@ -165,13 +165,21 @@ class ClipEncoder:
         entry[0].replay()
         return out
 
-    def _reserve(self, batch: int) -> None:
+    def _reserve(self, batch: int, lanes: int = 1) -> None:
         """Size the grow-only scratch buffers for ``batch`` clips up front, so that no chunk of a pipelined
-        run reallocates one while kernels of the previous chunk still use it."""
+        run reallocates one while kernels of the previous chunk still use it.  ``lanes`` > 1 reserves one set per
+        compute stream of the host-facing path (tags / mel slots ``...{lane}``)."""
         lib = self.rt.lib
-        self._mel_buf(batch)
-        self.rt.workspace("logmel", lib.yoho_logmel_workspace_bytes(batch, self.n_samples, self.n_fft, self.hop, self.n_mels))
-        self.rt.workspace("encoder", lib.yoho_encoder_workspace_bytes(C.byref(self.desc), batch, self.frames, self.compute))
+        lm = lib.yoho_logmel_workspace_bytes(batch, self.n_samples, self.n_fft, self.hop, self.n_mels)
+        en = lib.yoho_encoder_workspace_bytes(C.byref(self.desc), batch, self.frames, self.compute)
+        if lanes == 1:
+            self._mel_buf(batch)
+            self.rt.workspace("logmel", lm)
+            self.rt.workspace("encoder", en)
+        for lane in range(lanes if lanes > 1 else 0):
+            self._mel_buf(batch, slot=100 + lane)
+            self.rt.workspace(f"logmel{lane}", lm)
+            self.rt.workspace(f"encoder{lane}", en)
 
     # ---- host-facing path -------------------------------------------------------------------
     def host_buffers(self, batch: int, pcm_dtype: torch.dtype = torch.float32) -> tuple[torch.Tensor, torch.Tensor]:
@@ -196,8 +204,12 @@ class ClipEncoder:
         self.last_chunk_clips = chunk
         with torch.cuda.device(dev):
             if self._streams is None:
-                self._streams = tuple(torch.cuda.Stream(device=dev) for _ in range(3))
-            s_in, s_run, s_out = self._streams
+                self._streams = tuple(torch.cuda.Stream(device=dev) for _ in range(4))
+            # one copy stream per direction and TWO compute streams: chunk i runs on compute stream i & 1 with its own
+            # scratch, so the wave tails and launch gaps of one chunk's ~100 kernels are filled by the other chunk's
+            # (chunked like this without copies: 94.2 ms on one stream, 91.1 ms on two, 89.4 ms as a whole batch)
+            s_in, s_out, s_run0, s_run1 = self._streams
+            s_runs = (s_run0, s_run1)
             key = (chunk, pcm_host.dtype, out_host.dtype)
             st = self._stage.get(key)
             if st is None:
@@ -207,10 +219,9 @@ class ClipEncoder:
             entry = torch.cuda.current_stream(dev)
             ready = torch.cuda.Event()
             ready.record(entry)
-            for s in (s_in, s_run, s_out):
+            for s in (s_in, s_out, s_run0, s_run1):
                 s.wait_event(ready)
-            with torch.cuda.stream(s_run):
-                self._reserve(chunk)
+            self._reserve(chunk, lanes=2)
             ran: list = []
             drained: list = []
             for i, (b0, n) in enumerate(chunk_plan(B, chunk, taper)):
@@ -221,12 +232,13 @@ class ClipEncoder:
                     st["pcm"][slot][:n].copy_(pcm_host[b0:b1], non_blocking=True)
                     e_in = torch.cuda.Event()
                     e_in.record(s_in)
+                s_run = s_runs[slot]
                 with torch.cuda.stream(s_run):
                     s_run.wait_event(e_in)
                     if i >= 2:
                         s_run.wait_event(drained[i - 2])
-                    mel = self.logmel(st["pcm"][slot][:n], self._mel_buf(n))
-                    self.encoder(mel, st["out"][slot][:n])
+                    mel = self.logmel(st["pcm"][slot][:n], self._mel_buf(n, slot=100 + slot), ws_tag=f"logmel{slot}")
+                    self.encoder(mel, st["out"][slot][:n], ws_tag=f"encoder{slot}")
                     e_run = torch.cuda.Event()
                     e_run.record(s_run)
                     ran.append(e_run)
@@ -237,7 +249,8 @@ class ClipEncoder:
                     e_out.record(s_out)
                     drained.append(e_out)
             entry.wait_event(drained[-1])
-            entry.wait_event(ran[-1])
+            for e in ran[-2:]:
+                entry.wait_event(e)
             if sync:
                 drained[-1].synchronize()
         return out_host
