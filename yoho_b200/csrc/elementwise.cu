@@ -1,4 +1,4 @@
-// Memory-bound helpers of the encoder: LayerNorm, casts, weight packing, conv-stem im2col.
+// Memory-bound helpers of the encoder: LayerNorm, casts, weight packing / folding.
 #include "kernels.cuh"
 
 namespace yoho {
@@ -154,46 +154,6 @@ int launch_cast_f32(const __nv_bfloat16* src, float* dst, size_t n, cudaStream_t
   ProfScope prof(s, kProfOther, double(n) * 6.0);
   cast_f32_kernel<<<grid_for(n), 256, 0, s>>>(src, dst, n);
   YOHO_LAUNCH_CHECK("cast_f32_kernel");
-  return YOHO_OK;
-}
-
-// One CTA per (clip, group of rows): dst[b][t][tap*M + c] = mel[b][t+tap-1][c] (zero outside [0,F)),
-// columns 3M..k0-1 and rows F..Fp-1 zero.  Replaces the zero padding of nn.Conv(padding=1)
-// (whisper.py:125) so that Conv_0 becomes one plain K-major GEMM.
-__global__ void __launch_bounds__(256)
-mel_im2col_kernel(const float* __restrict__ mel, __nv_bfloat16* __restrict__ dst, int frames, int frames_padded, int n_mels, int k0) {
-  const int b = blockIdx.y;
-  const float* src = mel + size_t(b) * frames * n_mels;
-  __nv_bfloat16* out = dst + size_t(b) * frames_padded * k0;
-  const int rows_per_cta = 16;
-  const int t0 = blockIdx.x * rows_per_cta;
-  const int half = k0 >> 1;  // write bf16 pairs
-  for (int i = threadIdx.x; i < rows_per_cta * half; i += blockDim.x) {
-    int r = i / half, cp = i - r * half;
-    int t = t0 + r;
-    if (t >= frames_padded) break;
-    float v[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      int col = cp * 2 + e;
-      int tap = col / n_mels, c = col - tap * n_mels;
-      int ts = t + tap - 1;
-      v[e] = (t < frames && tap < 3 && ts >= 0 && ts < frames) ? __ldg(src + size_t(ts) * n_mels + c) : 0.0f;
-    }
-    __nv_bfloat162 p = __floats2bfloat162_rn(v[0], v[1]);
-    *reinterpret_cast<__nv_bfloat162*>(out + size_t(t) * k0 + cp * 2) = p;
-  }
-}
-int launch_mel_im2col(const float* mel, __nv_bfloat16* dst, int batch, int frames, int frames_padded, int n_mels, int k0, cudaStream_t s) {
-  if (k0 % 2 != 0 || k0 < 3 * n_mels) return fail(YOHO_ERR_INVALID, "mel_im2col: k0=%d", k0);
-  if (batch == 0) return YOHO_OK;
-  ProfScope prof(s, kProfOther, double(batch) * (double(frames) * n_mels * 4.0 + double(frames_padded) * k0 * 2.0));
-  for (int b0 = 0; b0 < batch; b0 += 65535) {
-    int nb = batch - b0 < 65535 ? batch - b0 : 65535;
-    mel_im2col_kernel<<<dim3(ceil_div(frames_padded, 16), nb), 256, 0, s>>>(
-        mel + size_t(b0) * frames * n_mels, dst + size_t(b0) * frames_padded * k0, frames, frames_padded, n_mels, k0);
-    YOHO_LAUNCH_CHECK("mel_im2col_kernel");
-  }
   return YOHO_OK;
 }
 

@@ -12,8 +12,6 @@ int launch_layernorm_bf16(const float* x, const float* scale, const float* bias,
 int launch_transpose_cast(const float* src, __nv_bfloat16* dst, int k, int n, int ld_dst, cudaStream_t s, int k_pad = -1);   // k_pad >= 0: zero only columns k..k_pad-1
 int launch_cast_bf16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t s);
 int launch_cast_f32(const __nv_bfloat16* src, float* dst, size_t n, cudaStream_t s);
-// mel (B, F, M) float32 -> (B, Fp, K0) bf16 rows [x[t-1], x[t], x[t+1], 0...]; rows t >= F are zero.
-int launch_mel_im2col(const float* mel, __nv_bfloat16* dst, int batch, int frames, int frames_padded, int n_mels, int k0, cudaStream_t s);
 int launch_fill_zero(void* p, size_t bytes, cudaStream_t s);
 
 // ---------------------------------------------------------------- yoho_ops.cu (YOHO's own encoder: model.py / layers.py)
