@@ -302,8 +302,15 @@ def main():
     # `value`: exactly K steps with nothing but the kernels between the two events (clocks sampled beside it).  The
     # rooflines come from a second pass of K steps with the library's per-launch event records switched on: ~100 event
     # pairs per step keep consecutive kernels from overlapping their launch, which costs 2-4 % (`ms_per_step_profiled`).
-    for _ in range(args.warmup):
+    # warm-up: at least W steps AND at least ~1.5 s of back-to-back steps, so that the power-capped clock has settled before
+    # the timed region (with 0.3 s of warm-up the first timed pass measured 2-3 % slower than an identical second pass)
+    t_warm = time.perf_counter()
+    n_warm = 0
+    while n_warm < args.warmup or (time.perf_counter() - t_warm < 1.5 and n_warm < 4000):
         step_device()
+        n_warm += 1
+        if n_warm % 4 == 0:
+            torch.cuda.synchronize()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -408,7 +415,7 @@ def main():
     line = {
         "metric": "audio-sec/sec (RTFx) log-mel+encoder" if stages == "logmel+encoder" else f"audio-sec/sec (RTFx) {stages}",
         "value": round(value, 1), "unit": "x realtime", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": round(ms_step, 4), "ms_per_step_profiled": round(ms_step_profiled, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": round(ms_step, 4), "ms_per_step_profiled": round(ms_step_profiled, 4), "warmup_steps_run": n_warm, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16" if "encoder" in stages else "f32", "data": "synthetic",
         "config": {"workload": desc, "model": model, "clips_per_gpu": clips, "global_clips": total_clips, "clip_seconds": CLIP_SECONDS,
                    "stages": stages, "norm": args.norm, "compute": "bf16 operands / fp32 accumulate (tcgen05); fp32 frontend, residual stream and LayerNorm",

@@ -31,6 +31,11 @@ int fail(int code, const char* fmt, ...) {
   return code;
 }
 
+bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("YOHO_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 // ---- launch counter + event profiler ---------------------------------------------------------
 static std::atomic<long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }

@@ -181,6 +181,8 @@ attention3_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat1
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, sm.tmem_slot, 0);
+  pdl_launch_dependents();
+  pdl_wait();                      // the prologue above overlaps the tail of the q | k | v GEMM
   const int n_steps = p.n_steps;
   const int stride = int(gridDim.x);
   const int n_my = int(blockIdx.x) < p.n_items ? (p.n_items - int(blockIdx.x) + stride - 1) / stride : 0;   // items of this CTA
@@ -421,7 +423,7 @@ int launch_attention3_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat1
   YOHO_CUDA_CHECK(cudaFuncSetAttribute(attention3_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(Smem))));
   const int grid = p.n_items < ctx->num_sms ? p.n_items : ctx->num_sms;
   ProfScope prof(s, kProfAttention, 4.0 * double(batch) * double(t) * double(t) * double(dims));
-  attention3_bf16_kernel<<<grid, kThreads, sizeof(Smem), s>>>(map, out, p);
+  YOHO_CUDA_CHECK(launch_pdl(attention3_bf16_kernel, dim3(grid), dim3(kThreads), sizeof(Smem), s, map, out, p));
   YOHO_LAUNCH_CHECK("attention3_bf16_kernel");
   return YOHO_OK;
 }

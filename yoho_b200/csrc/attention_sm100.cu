@@ -103,6 +103,8 @@ attention_bf16_kernel(const __grid_constant__ CUtensorMap map_qkv, __nv_bfloat16
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, sm.tmem_slot, 0);
+  pdl_launch_dependents();
+  pdl_wait();
   const int n_kv = p.n_kv, n_steps = p.n_steps;
   const int stride = int(gridDim.x);
   const int n_my = int(blockIdx.x) < p.n_items ? (p.n_items - int(blockIdx.x) + stride - 1) / stride : 0;   // items of this CTA
@@ -397,7 +399,7 @@ int launch_attention_bf16(yoho_ctx* ctx, const __nv_bfloat16* qkv, __nv_bfloat16
   YOHO_CUDA_CHECK(cudaFuncSetAttribute(attention_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(sizeof(AttSmem))));
   const int grid = p.n_items < ctx->num_sms ? p.n_items : ctx->num_sms;
   ProfScope prof(s, kProfAttention, 4.0 * double(batch) * double(t) * double(t) * double(dims));
-  attention_bf16_kernel<<<grid, kAttThreads, sizeof(AttSmem), s>>>(map, out, p);
+  YOHO_CUDA_CHECK(launch_pdl(attention_bf16_kernel, dim3(grid), dim3(kAttThreads), sizeof(AttSmem), s, map, out, p));
   YOHO_LAUNCH_CHECK("attention_bf16_kernel");
   return YOHO_OK;
 }

@@ -41,6 +41,28 @@ struct ProfScope {
   cudaStream_t stream; int slot;
 };
 
+// ---- programmatic dependent launch -----------------------------------------------------------------------------------
+// Kernels of the encoder chain are launched with the programmatic-stream-serialization attribute: kernel B may be
+// scheduled while its predecessor A is still running (on idle SMs, or SMs A's CTAs have left), runs its prologue (barrier
+// init, TMEM allocation, tensor-map prefetch) and then blocks in pdl_wait() until A has completed and its writes are
+// visible.  Every participating kernel calls pdl_launch_dependents() first thing and pdl_wait() before its first global
+// memory access (reads AND writes: a buffer it overwrites may still be read by A).  YOHO_PDL=0 launches them plainly.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+#endif
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 

@@ -19,6 +19,8 @@ template <typename OutT>
 __global__ void __launch_bounds__(256, 4)
 layernorm_kernel(const float* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ bias,
                  OutT* __restrict__ y, int rows, int dims) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -65,7 +67,7 @@ static int launch_layernorm(const float* x, const float* scale, const float* bia
   if (dims % 4 != 0 || dims > kLnMaxVec * 128) return fail(YOHO_ERR_UNSUPPORTED, "layernorm: dims=%d (need multiple of 4, <= %d)", dims, kLnMaxVec * 128);
   if (rows == 0) return YOHO_OK;
   ProfScope prof(s, kProfLayerNorm, double(rows) * double(dims) * double(sizeof(float) + sizeof(OutT)));
-  layernorm_kernel<OutT><<<ceil_div(rows, 8), 256, 0, s>>>(x, scale, bias, y, rows, dims);
+  YOHO_CUDA_CHECK(launch_pdl(layernorm_kernel<OutT>, dim3(ceil_div(rows, 8)), dim3(256), 0, s, x, scale, bias, y, rows, dims));
   YOHO_LAUNCH_CHECK("layernorm_kernel");
   return YOHO_OK;
 }
@@ -129,6 +131,8 @@ int launch_ln_fold(const float* src, const float* scale, const float* beta, cons
 }
 
 __global__ void cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n) {
+  pdl_launch_dependents();
+  pdl_wait();
   size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
   const size_t step = size_t(gridDim.x) * blockDim.x;
   if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
@@ -146,7 +150,7 @@ __global__ void cast_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __
 static int grid_for(size_t n) { size_t g = (n + 255) / 256; return int(g > 148 * 32 ? 148 * 32 : (g ? g : 1)); }
 int launch_cast_bf16(const float* src, __nv_bfloat16* dst, size_t n, cudaStream_t s) {
   ProfScope prof(s, kProfOther, double(n) * 6.0);
-  cast_bf16_kernel<<<grid_for(n), 256, 0, s>>>(src, dst, n);
+  YOHO_CUDA_CHECK(launch_pdl(cast_bf16_kernel, dim3(grid_for(n)), dim3(256), 0, s, src, dst, n));
   YOHO_LAUNCH_CHECK("cast_bf16_kernel");
   return YOHO_OK;
 }

@@ -293,6 +293,8 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
     stage_pcm_async<T>(reinterpret_cast<T*>(sm.slot[buf]), pcm, size_t(clip) * n_samples, tile * kFramesPerCta * kHop, valid, vec_ok != 0);
   };
 
+  pdl_launch_dependents();
+  pdl_wait();                      // the mel / statistics buffers this kernel overwrites may still be read by the previous step's kernels
   int item = blockIdx.x;
   if (item >= n_items) return;
   stage(item, 0);
@@ -588,6 +590,8 @@ normalize_apply_kernel(const float* __restrict__ src, float* __restrict__ dst, i
                        int take_log) {
   __shared__ double dred[2 * (kFinThreads / 32)];
   __shared__ float coef[2];
+  pdl_launch_dependents();
+  pdl_wait();
   const int clip = clip0 + blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const float2* st = stats + size_t(clip) * tiles_per_clip;
   if (norm == YOHO_NORM_REFERENCE) {
@@ -697,15 +701,15 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
       ProfScope prof(stream, kProfFrontend, double(nb) * (double(n_samples) * sizeof(T) + double(elems) * sizeof(float)));
       const long long items = (long long)nb * tiles;
       const int grid = int(items < 2LL * ctx->num_sms ? items : 2LL * ctx->num_sms);
-      kernel<<<grid, kThreads, sizeof(FrontendSmem<T>), stream>>>(
+      YOHO_CUDA_CHECK(launch_pdl(kernel, dim3(grid), dim3(kThreads), sizeof(FrontendSmem<T>), stream,
           pcm, n_samples, total_samples, frames, c0, int(items), fb->d_bands, fb->d_weights, fb->n_groups, fb->n_weights,
-          fb->n_mels, out, stats, tiles, vec_ok, vec_out);
+          fb->n_mels, out, stats, tiles, vec_ok, vec_out));
       YOHO_LAUNCH_CHECK("logmel_kernel");
     }
     if (norm != YOHO_NORM_NONE) {
       ProfScope prof(stream, kProfNormalize, double(nb) * double(elems) * 2.0 * sizeof(float));
-      normalize_apply_kernel<<<dim3(ceil_div(elems, kFinElemsPerCta), nb), kFinThreads, 0, stream>>>(
-          out, out, elems, stats, tiles, c0, norm, 0);
+      YOHO_CUDA_CHECK(launch_pdl(normalize_apply_kernel, dim3(ceil_div(elems, kFinElemsPerCta), nb), dim3(kFinThreads), 0, stream,
+          out, out, elems, stats, tiles, c0, norm, 0));
       YOHO_LAUNCH_CHECK("normalize_apply_kernel");
     }
   }
@@ -798,8 +802,8 @@ extern "C" int yoho_normalize_f32(yoho_ctx* ctx, const float* spec, int batch, i
     spec_stats_kernel<<<dim3(tiles, nb), kStatThreads, 0, stream>>>(spec + size_t(c0) * elems, elems,
                                                                    stats + size_t(c0) * tiles, tiles, norm);
     YOHO_LAUNCH_CHECK("spec_stats_kernel");
-    normalize_apply_kernel<<<dim3(ceil_div(elems, kFinElemsPerCta), nb), kFinThreads, 0, stream>>>(
-        spec, out, elems, stats, tiles, c0, norm, 1);
+    YOHO_CUDA_CHECK(launch_pdl(normalize_apply_kernel, dim3(ceil_div(elems, kFinElemsPerCta), nb), dim3(kFinThreads), 0, stream,
+        spec, out, elems, stats, tiles, c0, norm, 1));
     YOHO_LAUNCH_CHECK("normalize_apply_kernel");
   }
   return YOHO_OK;

@@ -191,6 +191,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive / TMA signal
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+  // everything above (barriers, TMEM, descriptor prefetch) may run while the previous kernel of the stream is finishing
+  pdl_launch_dependents();
+  pdl_wait();
 
   const int kblocks = p.n_taps * p.kblocks_per_tap;
 
@@ -505,7 +508,7 @@ static int launch_gemm_bn(yoho_ctx* ctx, const GemmBf16Args& a, cudaStream_t s) 
   const int max_clusters = ctx->num_sms / 2;
   const int clusters = p.total_tiles < max_clusters ? p.total_tiles : max_clusters;
   ProfScope prof(s, kProfGemm, 2.0 * double(a.batch) * double(a.rows_per_batch) * double(a.n) * double(a.flop_k > 0 ? a.flop_k : a.n_taps * a.k_per_tap));
-  gemm_bf16_kernel<BN, kLn, kDeep><<<2 * clusters, kGemmThreads, Cfg::kSmemBytes, s>>>(map_a, map_w, map_c, p);
+  YOHO_CUDA_CHECK(launch_pdl(gemm_bf16_kernel<BN, kLn, kDeep>, dim3(2 * clusters), dim3(kGemmThreads), size_t(Cfg::kSmemBytes), s, map_a, map_w, map_c, p));
   YOHO_LAUNCH_CHECK("gemm_bf16_kernel");
   return YOHO_OK;
 }
