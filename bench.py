@@ -400,6 +400,10 @@ def main():
                             f"{tj[dominant]['clips']} clips, scaled to {per_launch_clips:.0f} clips per launch")
     except Exception as exc:
         traffic_note = f"profiles/traffic.json unreadable: {exc!r}"
+    if dominant == "gemm_tcgen05" and "encoder" in stages and os.environ.get("YOHO_LN_FUSE", "1")[:1] != "0":
+        rooflines[dominant]["note"] = ("FLOP of the GEMMs over a time that also holds the work of the 2 LayerNorms per block folded into their epilogues "
+                                       "(residual rows fetched and re-stored, bf16 copy, row statistics); A/B on one box, profiles/r02_lnfuse.txt: "
+                                       "YOHO_LN_FUSE=0 gives gemm 1295 TFLOP/s (0.90) + 7.4 ms of LayerNorm kernels and a step 1.8 % slower")
     roofline = dict(rooflines[dominant], kernel=dominant, traffic=traffic, traffic_note=traffic_note,
                     peak_source=f"{pk['source']} ({'sustained bf16 cuBLAS' if rooflines[dominant]['bound'] == 'tensor' else 'copy bandwidth'}, MEASURED_PEAKS.json)") if dominant else None
 
