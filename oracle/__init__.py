@@ -21,7 +21,8 @@ of its own.  What pins this oracle:
   jax / flax names they use, and their outputs are committed as
   ``tests/golden/reference_shim_golden.npz``.  The oracle agrees with them to
   1e-13 (log-mel), 0.0 / 1e-11 (Whisper encoder, float64), bit-for-bit (sinusoid
-  table, float32) and 1e-7 relative (YOHO's encoder: complex64 RoPE factors).
+  table, float32), 1e-7 relative (YOHO's encoder: complex64 RoPE factors) and
+  0.0 (text decoder and the whole Whisper.__call__, float64).
   This pins what the reference's authors wrote -- composition, order, scales,
   transposes, einsum patterns, pytree names -- but NOT the inside of the
   library primitives (stft, Dense, Conv, LayerNorm, gelu, softmax, RMSNorm,

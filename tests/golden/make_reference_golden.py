@@ -18,6 +18,7 @@ import numpy as np
 ROOT = Path(__file__).resolve().parents[2]
 sys.path.insert(0, str(ROOT))
 
+from oracle import decoder as od  # noqa: E402
 from oracle import encoder as eo  # noqa: E402
 from oracle import refshim  # noqa: E402
 from oracle import yoho_model as ym  # noqa: E402
@@ -25,6 +26,13 @@ from oracle import yoho_model as ym  # noqa: E402
 GOLDEN = ROOT / "tests" / "golden"
 YOHO_SHAPE = dict(n_mels=64, dims=256, q_heads=4, kv_heads=2, blocks=2, frames=50, seed=7)   # head dim 64: what the CUDA path supports
 TABLE_SHAPES = [(1500, 384), (1500, 512), (1500, 768), (1500, 1280)]
+DECODER_SHAPE = dict(vocab=97, text_seq_len=24, dims=128, heads=2, layers=2, audio_frames=50, batch=3, tokens=11, seed=3)
+
+
+def as_float64(tree):
+    """Token ids carry no floating dtype, so a float64 run of the reference's decoder needs float64 leaves (float32 leaves
+    make it a float32 run: measured 7e-6 from the float64 oracle, pure rounding)."""
+    return {k: as_float64(v) for k, v in tree.items()} if isinstance(tree, dict) else np.asarray(tree, np.float64)
 
 
 def run_reference() -> dict:
@@ -66,6 +74,21 @@ def run_reference() -> dict:
     yenc = model.AudioEncoder(q_heads=s["q_heads"], kv_heads=s["kv_heads"], dims=s["dims"], seq_len=s["frames"], blocks=s["blocks"])
     out["yoho_mel"] = ymel.astype(np.float32)
     out["yoho_out"] = np.asarray(yenc.apply({"params": yparams}, ymel.astype(np.float32).astype(np.float64)))
+    # ---- text decoder: whisper.py:138-165 through Whisper.decode_text (:197-198) and the whole model (Whisper.__call__, :200-203)
+    d = DECODER_SHAPE
+    dparams = od.init_params(d["vocab"], d["text_seq_len"], d["dims"], d["layers"], seed=d["seed"])
+    rng = np.random.default_rng(d["seed"] + 1)
+    states = rng.standard_normal((d["batch"], d["audio_frames"], d["dims"])).astype(np.float32)
+    tokens = rng.integers(0, d["vocab"], (d["batch"], d["tokens"]))
+    aparams = eo.init_params(80, d["dims"], 1, seed=d["seed"])
+    dmel = rng.standard_normal((d["batch"], 2 * d["audio_frames"] - 1, 80)).astype(np.float32)
+    net = whisper.Whisper(audio_dims=d["dims"], audio_seq_len=d["audio_frames"], audio_heads=d["heads"], audio_layers=1,
+                          text_vocab_size=d["vocab"], text_seq_len=d["text_seq_len"], text_dims=d["dims"], text_heads=d["heads"],
+                          text_layers=d["layers"])
+    variables = {"params": {"audio_encoder": as_float64(aparams), "text_decoder": as_float64(dparams)}}
+    out["decoder_states"], out["decoder_tokens"], out["decoder_mel"] = states, tokens.astype(np.int32), dmel
+    out["decoder_logits"] = np.asarray(net.apply(variables, states.astype(np.float64), tokens, method=whisper.Whisper.decode_text))
+    out["whisper_logits"] = np.asarray(net.apply(variables, dmel.astype(np.float64), tokens))
     return {k: np.asarray(v) for k, v in out.items()}
 
 

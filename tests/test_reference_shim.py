@@ -16,6 +16,7 @@ import hashlib
 import numpy as np
 import pytest
 
+from oracle import decoder as od
 from oracle import encoder as eo
 from oracle import frontend as fo
 from oracle import refshim
@@ -140,6 +141,40 @@ def test_oracle_yoho_encoder_equals_reference(ref_golden):
     assert np.abs(got - want).max() <= 5e-6 * np.abs(want).max()
 
 
+def _decoder_case(mod):
+    d = mod.DECODER_SHAPE
+    return d, od.init_params(d["vocab"], d["text_seq_len"], d["dims"], d["layers"], seed=d["seed"]), eo.init_params(80, d["dims"], 1, seed=d["seed"])
+
+
+def test_oracle_decoder_equals_reference(ref_golden):
+    """TextDecoder (whisper.py:138-165) through Whisper.decode_text, and the whole model (Whisper.__call__, :200-203)."""
+    _, _, mod = _yoho_case()
+    d, dparams, aparams = _decoder_case(mod)
+    tokens = ref_golden["decoder_tokens"]
+    got = od.text_decoder(dparams, tokens, ref_golden["decoder_states"], d["heads"], np.float64)
+    assert np.abs(got - ref_golden["decoder_logits"]).max() <= 1e-11
+    states = eo.audio_encoder(aparams, ref_golden["decoder_mel"].astype(np.float64), d["heads"], np.float64)
+    got = od.text_decoder(dparams, tokens, states, d["heads"], np.float64)
+    assert np.abs(got - ref_golden["whisper_logits"]).max() <= 1e-10
+
+
+@needs_reference
+def test_live_decoder_float32_run(ref_golden):
+    """Token ids carry no floating dtype: with the float32 leaves a checkpoint holds, the reference's decoder code runs in
+    float32 and lands within float32 round-off of the float64 vectors."""
+    _, whisper, _, _ = refshim.load_reference()
+    _, _, mod = _yoho_case()
+    d, dparams, _ = _decoder_case(mod)
+    net = whisper.Whisper(audio_dims=d["dims"], audio_seq_len=d["audio_frames"], audio_heads=d["heads"], audio_layers=1,
+                          text_vocab_size=d["vocab"], text_seq_len=d["text_seq_len"], text_dims=d["dims"], text_heads=d["heads"],
+                          text_layers=d["layers"])
+    got = np.asarray(net.apply({"params": {"text_decoder": dparams}}, ref_golden["decoder_states"], ref_golden["decoder_tokens"],
+                               method=whisper.Whisper.decode_text))
+    want = ref_golden["decoder_logits"]
+    assert got.dtype == np.float32
+    assert 0 < np.abs(got - want).max() <= 1e-5 * np.abs(want).max()
+
+
 # ------------------------------------------------------------------ the CUDA path against the reference's outputs
 @pytest.fixture(scope="module")
 def gpu(built_library):
@@ -184,3 +219,23 @@ def test_gpu_yoho_encoder_vs_reference(gpu, ref_golden):
     assert np.abs(out32 - want).max() <= 1e-4 * max(1.0, float(np.abs(want).max()))
     out16 = enc.apply({"params": params}, ref_golden["yoho_mel"], compute="bf16")
     assert np.abs(out16 - want).max() / np.abs(want).max() <= 2e-2
+
+
+@pytest.mark.gpu
+def test_gpu_decoder_vs_reference(gpu, ref_golden):
+    """The float32 decoder kernels against the reference's decode_text output; then the whole model
+    (encoder float32 -> decoder) against Whisper.__call__'s."""
+    from yoho_b200.nn import Whisper
+    _, _, mod = _yoho_case()
+    d, dparams, aparams = _decoder_case(mod)
+    net = Whisper(audio_dims=d["dims"], audio_seq_len=d["audio_frames"], audio_heads=d["heads"], audio_layers=1,
+                  text_vocab_size=d["vocab"], text_seq_len=d["text_seq_len"], text_dims=d["dims"], text_heads=d["heads"],
+                  text_layers=d["layers"])
+    variables = {"params": {"audio_encoder": aparams, "text_decoder": dparams}}
+    tokens = ref_golden["decoder_tokens"].astype(np.int64)
+    want = ref_golden["decoder_logits"]
+    got = np.asarray(net.apply(variables, ref_golden["decoder_states"], tokens, method=Whisper.decode_text))
+    assert np.abs(got - want).max() <= 1e-4 * max(1.0, np.abs(want).max())
+    want = ref_golden["whisper_logits"]
+    got = np.asarray(net.apply(variables, ref_golden["decoder_mel"], tokens, compute="fp32"))
+    assert np.abs(got - want).max() <= 1e-4 * max(1.0, np.abs(want).max())
