@@ -1,11 +1,18 @@
 #!/bin/bash
-# Build an A/B copy of the library in which one translation unit is replaced by another source and/or compiled with
-# extra flags.  usage: tools/build_variant.sh <suffix> <unit: attention_sm100|gemm_sm100|...> <source> [nvcc flags...]
-#   -> yoho_b200/lib/libyoho_b200_<suffix>.so   (select it with YOHO_B200_LIB; the in-tree build must exist: build/obj)
-set -e
-sfx=$1; unit=$2; src=$3; shift 3
-mkdir -p build/ab
-nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr "$@" -I include -I yoho_b200/csrc -c $src -o build/ab/${unit}_$sfx.o
-objs=$(ls build/obj/*.o | grep -v "/$unit\.")
-nvcc -shared -gencode arch=compute_100a,code=sm_100a -o yoho_b200/lib/libyoho_b200_$sfx.so $objs build/ab/${unit}_$sfx.o -cudart static -Xlinker --exclude-libs=ALL
-echo yoho_b200/lib/libyoho_b200_$sfx.so
+# Build a variant of libyoho_b200.so for A/B timing: recompiles ONE source with extra -D flags and links it with the
+# objects of the regular build (build/obj).  usage: tools/build_variant.sh <name> <source.cu> <flags...>
+#   -> build/variants/libyoho_b200_<name>.so   (select it with YOHO_B200_LIB=<path>)
+set -euo pipefail
+name=$1; src=$2; shift 2
+root=$(cd "$(dirname "$0")/.." && pwd)
+mkdir -p "$root/build/variants"
+obj="$root/build/variants/${src}.${name}.o"
+nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr "$@" \
+  -c "$root/yoho_b200/csrc/$src" -o "$obj"
+objs=()
+for o in "$root"/build/obj/*.o; do
+  if [ "$(basename "$o")" = "${src}.o" ]; then objs+=("$obj"); else objs+=("$o"); fi
+done
+nvcc -shared -gencode arch=compute_100a,code=sm_100a -o "$root/build/variants/libyoho_b200_${name}.so" "${objs[@]}" \
+  -cudart static -Xlinker --exclude-libs=ALL -ldl
+echo "$root/build/variants/libyoho_b200_${name}.so"

@@ -335,6 +335,37 @@ def stage_attnperf():
               f"{us * 1e-6 * 1.9e9 * 148 / tiles:6.0f} SM-cycles@1.9GHz per 128x128 tile pair")
 
 
+def stage_attnsus():
+    """Attention kernel in the sustained (power-capped) regime: 256 clips of whisper-small, ~1.5 s of back-to-back
+    launches before the timed ones, so the SM clock is where the bench step finds it."""
+    import time
+    rt = get_runtime()
+    lib = rt.lib
+    batch, t, heads = 256, 1500, 12
+    qkv = torch.randn((batch, t, 3, heads, 64), device="cuda")
+    out = torch.empty((batch, t, heads * 64), device="cuda")
+    nbytes = lib.yoho_test_attention_workspace_bytes(batch, t, heads)
+    ws = rt.workspace("test", nbytes)
+
+    def run(n):
+        for _ in range(n):
+            check(lib.yoho_test_attention_bf16(rt.ctx, C.c_void_p(qkv.data_ptr()), C.c_void_p(out.data_ptr()), batch, t, heads,
+                                               C.c_void_p(rt.aligned_ptr(ws)), nbytes, rt.stream_ptr()))
+    t0 = time.time()
+    while time.time() - t0 < 1.5:
+        run(20)
+        torch.cuda.synchronize()
+    lib.yoho_prof_enable(1)
+    run(100)
+    torch.cuda.synchronize()
+    ncls = lib.yoho_prof_num_classes()
+    ms, work, cnt = (C.c_double * ncls)(), (C.c_double * ncls)(), (C.c_longlong * ncls)()
+    check(lib.yoho_prof_collect(ms, work, cnt, ncls))
+    lib.yoho_prof_enable(0)
+    a = 3
+    print(f"[attnsus] B{batch} T{t} H{heads} sustained: {ms[a] / cnt[a] * 1e3:8.1f} us  {work[a] / ms[a] / 1e9:7.1f} TFLOP/s  ({cnt[a]} launches)")
+
+
 def stage_attnphases():
     """Debug build only (YOHO_EXTRA_NVCC_FLAGS=-DYOHO_ATT_TIMING): clock64 totals of the softmax phases of CTA 0 / warp 0."""
     rt = get_runtime()
