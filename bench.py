@@ -60,15 +60,21 @@ class ClockSampler:
     """nvidia-smi sampler running beside the timed region (B200_PROFILING.md clocks line)."""
 
     QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,timestamp")
 
     def __init__(self, gpu_index: int):
-        self.gpu, self.proc = gpu_index, None
+        self.gpu, self.proc, self.t_mark = gpu_index, None, None
+
+    def mark(self):
+        """Only samples taken from now on count (the process is started during the warm-up: nvidia-smi's start-up is ~1 s of
+        driver activity that measurably slows the kernels it runs beside)."""
+        import datetime
+        self.t_mark = datetime.datetime.now()
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                                          "-lms", "200", "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
 
@@ -81,11 +87,23 @@ class ClockSampler:
         except subprocess.TimeoutExpired:
             self.proc.kill()
             out, _ = self.proc.communicate()
+        import datetime
+        lines = [[x.strip() for x in line.split(",")] for line in out.splitlines()]
+        lines = [f for f in lines if len(f) >= 9]
+
+        def inside(f):
+            if self.t_mark is None or len(f) < 10:
+                return True
+            try:
+                return datetime.datetime.strptime(f[9], "%Y/%m/%d %H:%M:%S.%f") >= self.t_mark
+            except ValueError:
+                return True
+        timed_lines = [f for f in lines if inside(f)]
+        window = "timed region"
+        if not timed_lines and lines:            # a timed region shorter than the sampling period: the warm-up just before it
+            timed_lines, window = lines[-5:], "end of warm-up + timed region (timed region shorter than the 0.2 s sampling period)"
         sm, smax, power, reasons = [], [], [], set()
-        for line in out.splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 9:
-                continue
+        for f in timed_lines:
             try:
                 sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
             except ValueError:
@@ -97,7 +115,7 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
         busy = [s for s, p in zip(sm, power) if p >= 0.5 * max(power)] or sm
         return {"sm_mhz": statistics.median(busy), "sm_max_mhz": max(smax), "power_w_max": max(power),
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
 # ------------------------------------------------------------------------------------------ CPU oracle timing
@@ -302,18 +320,23 @@ def main():
     # `value`: exactly K steps with nothing but the kernels between the two events (clocks sampled beside it).  The
     # rooflines come from a second pass of K steps with the library's per-launch event records switched on: ~100 event
     # pairs per step keep consecutive kernels from overlapping their launch, which costs 2-4 % (`ms_per_step_profiled`).
-    # warm-up: at least W steps AND at least ~1.5 s of back-to-back steps, so that the power-capped clock has settled before
+    # warm-up: at least W steps AND at least ~2.5 s of back-to-back steps, so that the power-capped clock has settled before
     # the timed region (with 0.3 s of warm-up the first timed pass measured 2-3 % slower than an identical second pass)
+    # The nvidia-smi sampler is started at the beginning of the warm-up (its start-up perturbs the kernels for about a second:
+    # the first timed pass measured 2.7 % slower than an identical pass without it) and samples at 5 Hz through the timed
+    # region; only the samples taken inside that region are reported.
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
     t_warm = time.perf_counter()
     n_warm = 0
-    while n_warm < args.warmup or (time.perf_counter() - t_warm < 1.5 and n_warm < 4000):
+    while n_warm < args.warmup or (time.perf_counter() - t_warm < 2.5 and n_warm < 4000):
         step_device()
         n_warm += 1
         if n_warm % 4 == 0:
             torch.cuda.synchronize()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    torch.cuda.synchronize()
+    sampler.mark()
     ms_plain_total, launches = timed(step_device, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     ms_step = ms_plain_total / args.steps
@@ -400,6 +423,10 @@ def main():
                             f"{tj[dominant]['clips']} clips, scaled to {per_launch_clips:.0f} clips per launch")
     except Exception as exc:
         traffic_note = f"profiles/traffic.json unreadable: {exc!r}"
+    for name, r in rooflines.items():
+        if r["bound"] == "hbm" and r["frac"] > 1.0:
+            r["note"] = ("algorithmic bytes over the measured copy bandwidth: above 1 because part of the kernel's input was written by the kernel "
+                         "before it and is still in the 126 MB L2 (measured DRAM traffic is below the algorithmic bytes)")
     if dominant == "gemm_tcgen05" and "encoder" in stages and os.environ.get("YOHO_LN_FUSE", "1")[:1] != "0":
         rooflines[dominant]["note"] = ("FLOP of the GEMMs over a time that also holds the work of the 2 LayerNorms per block folded into their epilogues "
                                        "(residual rows fetched and re-stored, bf16 copy, row statistics); A/B on one box, profiles/r02_lnfuse.txt: "
