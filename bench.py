@@ -87,15 +87,20 @@ class ClockSampler:
         except subprocess.TimeoutExpired:
             self.proc.kill()
             out, _ = self.proc.communicate()
+        return self.summarise(out, self.t_mark)
+
+    @staticmethod
+    def summarise(out: str, t_mark=None) -> dict:
+        """nvidia-smi csv lines -> the `clocks` object; only lines stamped at or after t_mark count (all, if none is)."""
         import datetime
         lines = [[x.strip() for x in line.split(",")] for line in out.splitlines()]
         lines = [f for f in lines if len(f) >= 9]
 
         def inside(f):
-            if self.t_mark is None or len(f) < 10:
+            if t_mark is None or len(f) < 10:
                 return True
             try:
-                return datetime.datetime.strptime(f[9], "%Y/%m/%d %H:%M:%S.%f") >= self.t_mark
+                return datetime.datetime.strptime(f[9], "%Y/%m/%d %H:%M:%S.%f") >= t_mark
             except ValueError:
                 return True
         timed_lines = [f for f in lines if inside(f)]

@@ -138,3 +138,28 @@ def test_chunk_plan_partitions_the_batch():
     assert [n for _, n in chunk_plan(256, 32)] == [8, 24, 32, 32, 32, 32, 32, 32, 16, 8, 8]
     assert [n for _, n in chunk_plan(64, 32)] == [8, 24, 16, 8, 8]
     assert [n for _, n in chunk_plan(48, 32, taper=True)] == [32, 16]
+
+
+def test_bench_clock_sampler_reports_only_the_timed_region():
+    """bench.py starts nvidia-smi during the warm-up and keeps the samples stamped inside the timed region; a region shorter
+    than the sampling period falls back to the last samples before it and says so."""
+    import datetime
+    import importlib.util
+    from pathlib import Path
+    spec = importlib.util.spec_from_file_location("bench_mod", Path(__file__).resolve().parents[1] / "bench.py")
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    rows = ["0, 1965, 1965, 310.0, 0x0, Not Active, Not Active, Not Active, Not Active, 2026/11/05 10:00:00.100",
+            "0, 1400, 1965, 990.0, 0x4, Not Active, Not Active, Not Active, Active, 2026/11/05 10:00:01.100",
+            "0, 1320, 1965, 995.0, 0x4, Not Active, Not Active, Not Active, Active, 2026/11/05 10:00:02.100",
+            "0, 1340, 1965, 991.0, 0x4, Not Active, Not Active, Not Active, Active, 2026/11/05 10:00:02.300"]
+    out = "\n".join(rows)
+    mark = datetime.datetime(2026, 11, 5, 10, 0, 2, 0)
+    c = bench.ClockSampler.summarise(out, mark)
+    assert c["samples"] == 2 and c["sm_mhz"] == 1330.0 and c["reasons"] == ["sw_power_cap"] and c["window"] == "timed region"
+    assert bench.ClockSampler.summarise(out, None)["samples"] == 4
+    late = bench.ClockSampler.summarise(out, datetime.datetime(2026, 11, 5, 10, 0, 3, 0))
+    assert late["samples"] == 4 and late["window"].startswith("end of warm-up")
+    hot = bench.ClockSampler.summarise(rows[1].replace("Not Active, Active, 2026", "Active, Active, 2026"), None)
+    assert "sw_thermal_slowdown" in hot["reasons"]
+    assert bench.ClockSampler.summarise("", None)["reasons"] == ["no samples"]
