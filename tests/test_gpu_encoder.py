@@ -385,16 +385,18 @@ def test_allgather_states_c_abi(rt):
         nccl.ncclCommDestroy(comm)
 
 
-def test_unfused_layernorm_path_still_matches(rt):
-    """YOHO_LN_FUSE=0 (read once per process) selects the stand-alone LayerNorm kernels and plain weights, the A/B
-    partner of the default path that folds LayerNorm_0 / LayerNorm_1 into the GEMMs around them.  Run it in a child
-    process on the small all-kernels script, which checks every result against the oracle."""
+@pytest.mark.parametrize("switch", ["YOHO_LN_FUSE", "YOHO_PDL"])
+def test_ab_switches_still_match_the_oracle(rt, switch):
+    """The documented A/B switches, each read once per process: YOHO_LN_FUSE=0 selects the stand-alone
+    LayerNorm kernels and plain weights instead of folding LayerNorm_0 / LayerNorm_1 into the GEMMs around them; YOHO_PDL=0
+    launches every kernel without programmatic stream serialisation (the `griddepcontrol` instructions become no-ops).  Run
+    in a child process on the small all-kernels script, which checks every result against the oracle."""
     import os
     import subprocess
     import sys
     from pathlib import Path
     root = Path(__file__).resolve().parents[1]
-    env = dict(os.environ, YOHO_LN_FUSE="0")
+    env = dict(os.environ, **{switch: "0"})
     r = subprocess.run([sys.executable, str(root / "tools" / "sanitize_case.py")], env=env, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "[sanitize] done" in r.stdout
