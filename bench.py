@@ -266,7 +266,7 @@ def main():
     enc = ClipEncoder((n_mels, dims, heads, layers if "encoder" in stages else 0), params, n_samples=N_SAMPLES,
                       norm=args.norm, compute="bf16", device=local_rank)
     pcm_host, out_host = enc.host_buffers(B)
-    pcm_host.copy_(torch.from_numpy(synth_batch(B, N_SAMPLES, first_index=lo, unique=8)))
+    pcm_host.copy_(torch.from_numpy(synth_batch(B, N_SAMPLES, first_index=lo, unique=min(B, 16), mix=True)))
     pcm_dev = pcm_host.to(dev)
     mel_dev = torch.empty((B, enc.frames, n_mels), dtype=torch.float32, device=dev)
     out_dev = torch.empty((B, enc.seq_len, dims), dtype=torch.float32, device=dev) if "encoder" in stages else None
@@ -459,7 +459,7 @@ def main():
                    "weights": "random-init (seed 42)", "cuda_graph": bool(use_graph),
                    "layernorm": ("folded into the GEMM epilogues on either side (gemm_tcgen05 time includes that work; only the final LayerNorm is a kernel)"
                                  if os.environ.get("YOHO_LN_FUSE", "1")[:1] != "0" else "stand-alone kernels (YOHO_LN_FUSE=0)"),
-                   "clips": "8 distinct synthetic clips per rank repeated with 16 gains (timing does not depend on content; parity tests use distinct clips)",
+                   "clips": f"{B} distinct synthetic clips per rank: 16 synthesised from scratch, the others each a mixture of two of them with a clip-specific rotation (yoho_b200.synth.synth_batch(mix=True))",
                    "l2": f"inputs larger than L2: {B * N_SAMPLES * 4 / 1e6:.0f} MB PCM per GPU per step, activations stream through HBM"},
         "e2e": {"value": round(e2e_value, 1), "unit": "x realtime", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": round(ms_e2e, 4), "chunk_clips": getattr(enc, "last_chunk_clips", args.e2e_chunk)},

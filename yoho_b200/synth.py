@@ -34,9 +34,10 @@ def synth_clip(index: int, n_samples: int = CLIP_SAMPLES, sample_rate: int = SAM
 
 
 def synth_batch(n_clips: int, n_samples: int = CLIP_SAMPLES, first_index: int = 0,
-                unique: int | None = None) -> np.ndarray:
-    """(n_clips, n_samples) float32.  ``unique`` bounds the number of distinct clips that are
-    synthesised (the rest are gain-scaled repeats) so that large benchmark batches build quickly."""
+                unique: int | None = None, mix: bool = False) -> np.ndarray:
+    """(n_clips, n_samples) float32.  ``unique`` bounds the number of clips that are synthesised from scratch so that
+    large benchmark batches build quickly; the others are gain-scaled repeats of them, or, with ``mix``, DISTINCT clips:
+    a synthesised clip plus a quarter of another one rotated by a clip-specific number of samples."""
     unique = n_clips if unique is None else max(1, min(unique, n_clips))
     base = np.stack([synth_clip(first_index + i, n_samples) for i in range(unique)])
     if unique == n_clips:
@@ -44,5 +45,9 @@ def synth_batch(n_clips: int, n_samples: int = CLIP_SAMPLES, first_index: int = 
     out = np.empty((n_clips, n_samples), np.float32)
     for i in range(n_clips):
         gain = np.float32(1.0 - 0.03125 * ((i // unique) % 16))
-        out[i] = base[i % unique] * gain
+        if mix and i >= unique:
+            g = first_index + i
+            out[i] = base[i % unique] * np.float32(0.75 * gain) + np.float32(0.25) * np.roll(base[(7 * i + 3) % unique], 997 * g + 131)
+        else:
+            out[i] = base[i % unique] * gain
     return out
