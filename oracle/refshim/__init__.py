@@ -14,7 +14,8 @@ the order and composition of operations, every scale factor and transpose, which
 patterns, the parameter pytree's names (they come out of the reference's module structure through Flax's auto-naming rules,
 restated in the shim).  What it cannot pin is the inside of the library primitives (stft, Dense, Conv, LayerNorm, gelu,
 softmax, RMSNorm, max_pool): those are the shim's restatement of the documented jax 0.4.28 / flax 0.8.4 / scipy behaviour
-(stft is SciPy's own).  ``tests/golden/make_reference_golden.py`` runs the reference this way and commits its outputs as
+(stft is SciPy's own); ``tests/test_refshim_primitives.py`` holds each of them to torch's implementation of the same operation.
+``tests/golden/make_reference_golden.py`` runs the reference this way and commits its outputs as
 ``tests/golden/reference_shim_golden.npz``; ``tests/test_reference_shim.py`` checks the oracle (and, on the GPU, the CUDA
 path) against them.  ``/root/reference`` does not exist on the GPU box: only the committed vectors travel.
 """
