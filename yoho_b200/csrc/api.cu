@@ -182,21 +182,44 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return len[a] > len[b]; });
   // |2 X[k]|^2 comes out of the packed-pair FFT; stft scales by 1/sum(w) (scaling='spectrum').
   const double scale = 0.25 / (ctx->window_sum * ctx->window_sum);
-  // groups of four bands (longest first) share one trip count: a warp walks two bands per half warp at a time
-  const int n_groups = (n_mels + kMelGroup - 1) / kMelGroup;
-  std::vector<int4> bands(size_t(kMelGroup) * n_groups);
+  // Groups of eight bands (longest first) share one trip count: one warp-round of the kernel's mel phase.  The groups are
+  // dealt to the CTA's five warps longest-processing-time first and stored [round][warp]; a warp without a group in a round
+  // finds a filler (trip 0).
+  const int n_real = (n_mels + kMelGroup - 1) / kMelGroup;
+  std::vector<int> trips(n_real);
+  for (int g = 0; g < n_real; ++g) {
+    trips[g] = (len[order[kMelGroup * g]] + 1) & ~1;              // the group's longest band comes first; walked two bins a step
+    if (trips[g] > n_bins - (n_bins & 1)) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: band of %d bins", len[order[kMelGroup * g]]);
+  }
+  std::vector<std::vector<int>> mine(kMelWarps);
+  std::vector<int> load(kMelWarps, 0);
+  for (int g = 0; g < n_real; ++g) {                              // trips are already in descending order
+    int best = 0;
+    for (int wv = 1; wv < kMelWarps; ++wv) if (load[wv] < load[best]) best = wv;
+    mine[best].push_back(g);
+    load[best] += trips[g] / 2 + 2;                               // steps + the round's fixed cost
+  }
+  size_t rounds = 0;
+  for (const auto& v : mine) rounds = v.size() > rounds ? v.size() : rounds;
+  if (rounds > size_t(kMelMaxRounds)) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: %zu rounds of band groups", rounds);
+  const int n_groups = n_real;
+  std::vector<int4> bands(size_t(kMelGroup) * n_groups + 8, make_int4(-1, -1, -1, -1));   // descriptors, then schedule[32]
+  int* sched = reinterpret_cast<int*>(bands.data() + size_t(kMelGroup) * n_groups);
+  for (size_t r = 0; r < rounds; ++r)
+    for (int wv = 0; wv < kMelWarps; ++wv)
+      if (r < mine[wv].size()) sched[r * kMelWarps + wv] = mine[wv][r];
   std::vector<float2> w;
   for (int g = 0; g < n_groups; ++g) {
-    const int trip = (len[order[kMelGroup * g]] + 1) & ~1;        // the group's longest band comes first; walked two bins a step
-    if (trip > n_bins - (n_bins & 1)) return fail(YOHO_ERR_UNSUPPORTED, "yoho_filterbank_create: band of %d bins", len[order[kMelGroup * g]]);
+    const int trip = trips[g];
+    int4* dst = bands.data() + size_t(kMelGroup) * g;
     for (int h = 0; h < kMelGroup; ++h) {
-      const int r = kMelGroup * g + h;
-      if (r >= n_mels) { bands[r] = make_int4(-1, 0, int(w.size()) - trip, trip); continue; }   // filler: walks its neighbour's weights, stores nothing
-      const int m = order[r];
+      const int idx = kMelGroup * g + h;
+      if (idx >= n_mels) { dst[h] = make_int4(-1, 0, int(w.size()) - trip, trip); continue; }   // walks its neighbour's weights, stores nothing
+      const int m = order[idx];
       const int first = lo[m] + trip <= n_bins ? lo[m] : n_bins - trip;   // keep the walk inside the power tile
-      bands[r] = make_int4(m, first, int(w.size()), trip);
-      for (int j = 0; j < trip; ++j) {
-        const int k = first + j;
+      dst[h] = make_int4(m, first, int(w.size()), trip);
+      for (int jj = 0; jj < trip; ++jj) {
+        const int k = first + jj;
         const float v = (k >= lo[m] && k < lo[m] + len[m]) ? float(double(host_filters[size_t(m) * n_bins + k]) * scale) : 0.0f;
         w.push_back(make_float2(v, v));
       }
@@ -211,6 +234,7 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
   fb->n_mels = n_mels;
   fb->n_bins = n_bins;
   fb->n_groups = n_groups;
+  fb->n_rounds = int(rounds);
   fb->n_weights = int(w.size());
   fb->power_scale = scale;
   cudaError_t e;

@@ -105,13 +105,16 @@ int frontend_upload_constants(double* window_sum);
 constexpr int kMelMaxBands = 128;      // n_mels <= 128 (band pairs * 2)
 constexpr int kMelMaxWeights = 600;    // (w, w) entries held in shared memory: sum over bands of their pair's trip
 constexpr int kMelBins = 201;          // n_fft / 2 + 1
-constexpr int kMelGroup = 4;           // bands that share a trip count (two per half warp, interleaved)
+constexpr int kMelGroup = 8;           // bands that share a trip count: one warp-round of the mel phase (4 lane slots x 2)
+constexpr int kMelWarps = 5;           // warps of the frontend CTA: the host lays the groups out as [round][warp]
+constexpr int kMelMaxRounds = 6;       // rounds x kMelWarps schedule entries (32 bytes of shared memory)
 struct yoho_filterbank {
   int device = -1;
   int n_mels = 0, n_bins = 0;
   int n_groups = 0;           // groups of kMelGroup bands, sorted by trip (descending)
+  int n_rounds = 0;           // rounds of the mel phase: schedule[round][warp] = group or -1 (longest-processing-time first)
   int n_weights = 0;          // float2 entries in d_weights
-  int4* d_bands = nullptr;    // [kMelGroup * n_groups] {mel row or -1, first bin walked, offset into d_weights, trip}
+  int4* d_bands = nullptr;    // [kMelGroup * n_groups] {mel row or -1, first bin walked, offset into d_weights, trip}, then 8 int4 = the schedule
   float2* d_weights = nullptr; // (w, w) per walked bin, already multiplied by the STFT power scale
   double power_scale = 0.0;   // 0.25 / window_sum^2 folded into d_weights
 };

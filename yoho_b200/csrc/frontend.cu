@@ -85,9 +85,11 @@ struct FrontendSmem {
   float2 win[10][20];                         // which shared memory broadcasts in one wavefront and the constant cache serialises
   alignas(16) float2 mel_w[kMelMaxWeights];   // (w, w) per walked bin (resident for the whole kernel)
   int4 mel_band[kMelMaxBands];
+  signed char mel_sched[32];                  // [round][warp] -> group or -1
   float red[2 * 32];
 };
 static_assert(kFramesPerCta * kMelMaxBands * 4 <= kERows * kFftsPerCta * 4, "the output tile overlays e_re");
+static_assert(kWarps == kMelWarps, "the filterbank's [round][warp] layout is built for this CTA");
 
 // ---- two complex numbers in packed fp32 pairs (structure of arrays) -------------------------------------------------
 struct C2 { uint64_t re, im; };
@@ -173,6 +175,9 @@ __device__ __forceinline__ uint64_t lds_u64(uint32_t addr) {
   asm volatile("ld.shared.b64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
   return v;
 }
+__device__ __forceinline__ void lds_2u64(uint32_t addr, uint64_t& lo, uint64_t& hi) {
+  asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "r"(addr) : "memory");
+}
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
   float4 v;
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
@@ -227,35 +232,42 @@ __device__ __forceinline__ void stage_pcm_async(T* dst, const T* __restrict__ pc
 // E[block][pos][fft]: the element of column n2 sits at row block * 21 + pos(n2), pos = n2 / 2 + 10 * (n2 & 1)
 __device__ __forceinline__ int e_index(int block, int pos, int fft) { return (block * kEBlockRows + pos) * kFftsPerCta + fft; }
 
-// One frame pair against two bands (this half warp's two bands of a group; the other half warp has the other two):
+// Four frames (two packed pairs) against two bands (slots b and b + 4 of the warp's group of eight):
 // sum_i P[first + i][frames] * w_i over kSteps x 2 bins each.  a0 / a1 address the even / odd steps' rows of a band (odd
-// bins keep their 16-frame halves exchanged), wa its (w, w) table.  All loads first, with immediate offsets; four
+// bins keep their 16-frame halves exchanged), wa its (w, w) table.  All loads first (128-bit, immediate offsets); eight
 // independent accumulation chains.
 struct MelBandAddr { uint32_t a0, a1, wa; };
 template <int kSteps>
-__device__ __forceinline__ void mel_quad(const MelBandAddr& x, const MelBandAddr& y, uint64_t& sum_x, uint64_t& sum_y) {
-  uint64_t xp0[kSteps], xp1[kSteps], yp0[kSteps], yp1[kSteps];
+__device__ __forceinline__ void mel_oct(const MelBandAddr& x, const MelBandAddr& y, uint64_t (&sum_x)[2], uint64_t (&sum_y)[2]) {
+  uint64_t xa[kSteps][2], xb[kSteps][2], ya[kSteps][2], yb[kSteps][2];     // [step][frame pair] of the even / odd bin
   float4 xw[kSteps], yw[kSteps];
 #pragma unroll
   for (int i = 0; i < kSteps; ++i) {
-    xp0[i] = lds_u64(x.a0 + uint32_t(i) * (2 * kPRow * 4));
-    xp1[i] = lds_u64(x.a1 + uint32_t(i) * (2 * kPRow * 4));
+    lds_2u64(x.a0 + uint32_t(i) * (2 * kPRow * 4), xa[i][0], xa[i][1]);
+    lds_2u64(x.a1 + uint32_t(i) * (2 * kPRow * 4), xb[i][0], xb[i][1]);
     xw[i] = lds_f4(x.wa + uint32_t(i) * 16u);                 // (w_2i, w_2i, w_2i+1, w_2i+1)
-    yp0[i] = lds_u64(y.a0 + uint32_t(i) * (2 * kPRow * 4));
-    yp1[i] = lds_u64(y.a1 + uint32_t(i) * (2 * kPRow * 4));
+    lds_2u64(y.a0 + uint32_t(i) * (2 * kPRow * 4), ya[i][0], ya[i][1]);
+    lds_2u64(y.a1 + uint32_t(i) * (2 * kPRow * 4), yb[i][0], yb[i][1]);
     yw[i] = lds_f4(y.wa + uint32_t(i) * 16u);
   }
-  uint64_t s0 = mul_f32x2(xp0[0], pack_f32x2(xw[0].x, xw[0].y)), s1 = mul_f32x2(xp1[0], pack_f32x2(xw[0].z, xw[0].w));
-  uint64_t t0 = mul_f32x2(yp0[0], pack_f32x2(yw[0].x, yw[0].y)), t1 = mul_f32x2(yp1[0], pack_f32x2(yw[0].z, yw[0].w));
+  uint64_t s[4], t[4];
+  {
+    const uint64_t xw0 = pack_f32x2(xw[0].x, xw[0].y), xw1 = pack_f32x2(xw[0].z, xw[0].w);
+    const uint64_t yw0 = pack_f32x2(yw[0].x, yw[0].y), yw1 = pack_f32x2(yw[0].z, yw[0].w);
+    s[0] = mul_f32x2(xa[0][0], xw0); s[1] = mul_f32x2(xa[0][1], xw0); s[2] = mul_f32x2(xb[0][0], xw1); s[3] = mul_f32x2(xb[0][1], xw1);
+    t[0] = mul_f32x2(ya[0][0], yw0); t[1] = mul_f32x2(ya[0][1], yw0); t[2] = mul_f32x2(yb[0][0], yw1); t[3] = mul_f32x2(yb[0][1], yw1);
+  }
 #pragma unroll
   for (int i = 1; i < kSteps; ++i) {
-    s0 = fma_f32x2(xp0[i], pack_f32x2(xw[i].x, xw[i].y), s0);
-    s1 = fma_f32x2(xp1[i], pack_f32x2(xw[i].z, xw[i].w), s1);
-    t0 = fma_f32x2(yp0[i], pack_f32x2(yw[i].x, yw[i].y), t0);
-    t1 = fma_f32x2(yp1[i], pack_f32x2(yw[i].z, yw[i].w), t1);
+    const uint64_t xw0 = pack_f32x2(xw[i].x, xw[i].y), xw1 = pack_f32x2(xw[i].z, xw[i].w);
+    const uint64_t yw0 = pack_f32x2(yw[i].x, yw[i].y), yw1 = pack_f32x2(yw[i].z, yw[i].w);
+    s[0] = fma_f32x2(xa[i][0], xw0, s[0]); s[1] = fma_f32x2(xa[i][1], xw0, s[1]);
+    s[2] = fma_f32x2(xb[i][0], xw1, s[2]); s[3] = fma_f32x2(xb[i][1], xw1, s[3]);
+    t[0] = fma_f32x2(ya[i][0], yw0, t[0]); t[1] = fma_f32x2(ya[i][1], yw0, t[1]);
+    t[2] = fma_f32x2(yb[i][0], yw1, t[2]); t[3] = fma_f32x2(yb[i][1], yw1, t[3]);
   }
-  sum_x = add_f32x2(sum_x, add_f32x2(s0, s1));
-  sum_y = add_f32x2(sum_y, add_f32x2(t0, t1));
+  sum_x[0] = add_f32x2(sum_x[0], add_f32x2(s[0], s[2])); sum_x[1] = add_f32x2(sum_x[1], add_f32x2(s[1], s[3]));
+  sum_y[0] = add_f32x2(sum_y[0], add_f32x2(t[0], t[2])); sum_y[1] = add_f32x2(sum_y[1], add_f32x2(t[1], t[3]));
 }
 
 // |2 X_A[k]|^2 and |2 X_B[k]|^2 from a = Z[k], b = Z[400 - k] (frames A, B packed as re / im of one complex FFT)
@@ -269,7 +281,7 @@ __device__ __forceinline__ float2 untangle_power(float ax, float ay, float bx, f
 template <typename T, int kNorm>
 __global__ void __launch_bounds__(kThreads, 2)
 logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples, int n_frames, int clip0, int n_items,
-              const int4* __restrict__ fb_bands, const float2* __restrict__ fb_w, int n_groups, int n_weights, int n_mels,
+              const int4* __restrict__ fb_bands, const float2* __restrict__ fb_w, int n_groups, int n_rounds, int n_weights, int n_mels,
               float* __restrict__ out, float2* __restrict__ stats, int tiles_per_clip, int vec_ok, int vec_out) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   using Smem = FrontendSmem<T>;
@@ -281,7 +293,6 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
   const int fft = (lane & 7) + 8 * (lane >> 4);
   const int task = 2 * warp + ((lane >> 3) & 1);          // pass 1: columns 2 task, 2 task + 1; pass 2: columns task, 20 - task
   // mel roles: half warp h takes band h of the warp's current band pair, lane = frame pair
-  const int fp = lane & 15, mh = lane >> 4;
   const float log_floor = (kNorm == YOHO_NORM_WHISPER) ? 1e-10f : 1e-13f;
   constexpr int kWin = sizeof(T) == 2 ? 1 : 0;
 
@@ -303,6 +314,7 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
   for (int i = tid; i < 10 * 20; i += kThreads) (&sm.win[0][0])[i] = (&c_win[kWin][0][0])[i];
   for (int i = tid; i < n_weights; i += kThreads) sm.mel_w[i] = __ldg(fb_w + i);
   for (int i = tid; i < kMelGroup * n_groups; i += kThreads) sm.mel_band[i] = __ldg(fb_bands + i);
+  if (tid < 32) sm.mel_sched[tid] = static_cast<signed char>(__ldg(reinterpret_cast<const int*>(fb_bands + kMelGroup * n_groups) + tid));
 
   // statistics of the tile finished last: its per-warp partials sit in red[]; warp 0 adds them once a barrier has passed
   int pending_stats = -1;
@@ -411,53 +423,42 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
       }
     }
     __syncthreads();
-    // ---- banded mel projection: lane = frame pair, four bands per warp and step (two per half warp, interleaved) -------
+    // ---- banded mel projection: lane = (four frames, band slot); a warp walks a group of eight bands per round ---------
     const int frame0 = tile * kFramesPerCta;
     // output tile [mel][32 frames] of mel POWER; E is dead: every thread loaded its rows before the barrier
     float* otile = sm.e_re;
     {
       const uint32_t pbase = ptx::smem_u32(sm.slot[buf]), wbase = ptx::smem_u32(sm.mel_w);
-      const uint32_t col_even = uint32_t(2 * fp) * 4u, col_odd = uint32_t((2 * fp) ^ 16) * 4u;   // odd bins keep their halves exchanged
-      auto address = [&](const int4& band) {
-        const bool odd = band.y & 1;
-        return MelBandAddr{pbase + uint32_t(band.y) * (kPRow * 4) + (odd ? col_odd : col_even),
-                           pbase + uint32_t(band.y + 1) * (kPRow * 4) + (odd ? col_even : col_odd), wbase + uint32_t(band.z) * 8u};
+      const int fq = lane & 7, slot = lane >> 3;               // frames 4 fq .. 4 fq + 3; bands `slot` and `slot + 4` of the group
+      const uint32_t col = uint32_t(fq) * 16u;
+      auto address = [&](const int4& band) {                   // odd bins keep their 16-frame halves exchanged (64 bytes)
+        const uint32_t odd = uint32_t(band.y & 1) << 6, row = pbase + uint32_t(band.y) * (kPRow * 4);
+        return MelBandAddr{row + (col ^ odd), row + (kPRow * 4) + (col ^ odd ^ 64u), wbase + uint32_t(band.z) * 8u};
       };
-      auto group_of = [&](int round) { return round * kWarps + ((round & 1) ? kWarps - 1 - warp : warp); };   // longest first, boustrophedon
-      // descriptors {mel row, first bin, weight offset, trip} are fetched one round ahead
-      int4 nx = sm.mel_band[kMelGroup * min(group_of(0), n_groups - 1) + mh], ny = sm.mel_band[kMelGroup * min(group_of(0), n_groups - 1) + 2 + mh];
-      for (int round = 0; round * kWarps < n_groups; ++round) {
-        const int gi = group_of(round);
-        if (gi >= n_groups) break;
-        const int4 bx = nx, by = ny;
-        {
-          const int gn = min(group_of(round + 1), n_groups - 1);
-          nx = sm.mel_band[kMelGroup * gn + mh];
-          ny = sm.mel_band[kMelGroup * gn + 2 + mh];
-        }
+      // the host has dealt the groups to the five warps (longest processing time first): schedule[round][warp]
+      for (int round = 0; round < n_rounds; ++round) {
+        const int group = sm.mel_sched[round * kWarps + warp];
+        if (group < 0) continue;
+        const int4 bx = sm.mel_band[kMelGroup * group + slot], by = sm.mel_band[kMelGroup * group + 4 + slot];
+        int steps = bx.w >> 1;                                  // two bins a step; the same for the eight bands of the group
+        if (steps == 0) continue;
         MelBandAddr ax = address(bx), ay = address(by);
-        int steps = bx.w >> 1;                                  // two bins a step; the same for the four bands of the group
-        uint64_t sum_x = 0ull, sum_y = 0ull;
-        // one straight-line variant per step count (bands of the reference filterbanks have at most 14 bins); longer
-        // bands (other filterbanks) take chunks of seven steps first
-        while (steps > 7) {
-          mel_quad<7>(ax, ay, sum_x, sum_y);
-          ax.a0 += 7 * 2 * kPRow * 4; ax.a1 += 7 * 2 * kPRow * 4; ax.wa += 7 * 16;
-          ay.a0 += 7 * 2 * kPRow * 4; ay.a1 += 7 * 2 * kPRow * 4; ay.wa += 7 * 16;
-          steps -= 7;
+        uint64_t sum_x[2] = {0ull, 0ull}, sum_y[2] = {0ull, 0ull};
+        // one straight-line variant per step count up to four; longer bands take chunks of four steps first
+        while (steps > 4) {
+          mel_oct<4>(ax, ay, sum_x, sum_y);
+          ax.a0 += 4 * 2 * kPRow * 4; ax.a1 += 4 * 2 * kPRow * 4; ax.wa += 4 * 16;
+          ay.a0 += 4 * 2 * kPRow * 4; ay.a1 += 4 * 2 * kPRow * 4; ay.wa += 4 * 16;
+          steps -= 4;
         }
         switch (steps) {
-          case 1: mel_quad<1>(ax, ay, sum_x, sum_y); break;
-          case 2: mel_quad<2>(ax, ay, sum_x, sum_y); break;
-          case 3: mel_quad<3>(ax, ay, sum_x, sum_y); break;
-          case 4: mel_quad<4>(ax, ay, sum_x, sum_y); break;
-          case 5: mel_quad<5>(ax, ay, sum_x, sum_y); break;
-          case 6: mel_quad<6>(ax, ay, sum_x, sum_y); break;
-          case 7: mel_quad<7>(ax, ay, sum_x, sum_y); break;
-          default: break;
+          case 1: mel_oct<1>(ax, ay, sum_x, sum_y); break;
+          case 2: mel_oct<2>(ax, ay, sum_x, sum_y); break;
+          case 3: mel_oct<3>(ax, ay, sum_x, sum_y); break;
+          default: mel_oct<4>(ax, ay, sum_x, sum_y); break;
         }
-        if (bx.x >= 0) *reinterpret_cast<uint64_t*>(otile + bx.x * kFramesPerCta + 2 * fp) = sum_x;
-        if (by.x >= 0) *reinterpret_cast<uint64_t*>(otile + by.x * kFramesPerCta + 2 * fp) = sum_y;
+        if (bx.x >= 0) *reinterpret_cast<ulonglong2*>(otile + bx.x * kFramesPerCta + 4 * fq) = make_ulonglong2(sum_x[0], sum_x[1]);
+        if (by.x >= 0) *reinterpret_cast<ulonglong2*>(otile + by.x * kFramesPerCta + 4 * fq) = make_ulonglong2(sum_y[0], sum_y[1]);
       }
     }
     __syncthreads();
@@ -702,7 +703,7 @@ static int logmel_launch(yoho_ctx* ctx, const yoho_filterbank* fb, const T* pcm,
       const long long items = (long long)nb * tiles;
       const int grid = int(items < 2LL * ctx->num_sms ? items : 2LL * ctx->num_sms);
       YOHO_CUDA_CHECK(launch_pdl(kernel, dim3(grid), dim3(kThreads), sizeof(FrontendSmem<T>), stream,
-          pcm, n_samples, total_samples, frames, c0, int(items), fb->d_bands, fb->d_weights, fb->n_groups, fb->n_weights,
+          pcm, n_samples, total_samples, frames, c0, int(items), fb->d_bands, fb->d_weights, fb->n_groups, fb->n_rounds, fb->n_weights,
           fb->n_mels, out, stats, tiles, vec_ok, vec_out));
       YOHO_LAUNCH_CHECK("logmel_kernel");
     }
