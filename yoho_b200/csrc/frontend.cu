@@ -30,8 +30,9 @@
 //     (|2 X_A[k]|^2, |2 X_B[k]|^2 = U^2 + V^2 with U, V sums / differences of the halves): no Z round trip through shared
 //     memory.  Columns 0 and 10 are their own partners and take a scalar variant in one half warp.
 //   * Power goes to shared memory bin-major over the (dead) PCM tile; the mel bands (<= 2 filters touch any FFT bin) are
-//     applied with lane = frame PAIR (packed FMA) and two bands per warp, longest first; the (32 frames x n_mels) result is
-//     transposed through shared memory so the global stores are full 128-byte lines.
+//     applied with lane = (four frames, band slot): a warp walks a group of eight bands per round (packed FMA on two frame
+//     pairs, 128-bit loads), the groups dealt to the warps by the host; the (32 frames x n_mels) result is transposed
+//     through shared memory so the global stores are full 128-byte lines.
 //   * Persistent CTAs (two per SM) walk the (clip, tile) list; the PCM of the next tile arrives by 16-byte zero-filling
 //     cp.async into the other slot while the current tile is transformed (int16 is converted when it is read).
 #include "common.cuh"
