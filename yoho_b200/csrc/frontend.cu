@@ -317,8 +317,19 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
   for (int i = tid; i < kMelGroup * n_groups; i += kThreads) sm.mel_band[i] = __ldg(fb_bands + i);
   if (tid < 32) sm.mel_sched[tid] = static_cast<signed char>(__ldg(reinterpret_cast<const int*>(fb_bands + kMelGroup * n_groups) + tid));
 
-  // statistics of the tile finished last: its per-warp partials sit in red[]; warp 0 adds them once a barrier has passed
+  // statistics of the tile finished last: every thread carries its partial sums into the next iteration, where the warp
+  // reduction (a chain of five dependent shuffles, 6 % of the kernel's stall samples when it sat at the end of the output
+  // phase) runs before the first barrier, i.e. where the warps wait for the slowest one anyway; warp 0 adds the per-warp
+  // partials from red[] once that barrier has passed
   int pending_stats = -1;
+  float acc_sum = 0.0f, acc_sq = 0.0f, acc_max = -INFINITY;
+  auto reduce_warp_stats = [&]() {
+    if (kNorm == YOHO_NORM_NONE || pending_stats < 0) return;
+    const float a = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sum) : warp_max(acc_max);
+    const float b = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sq) : 0.0f;
+    if (lane == 0) { sm.red[warp] = a; sm.red[32 + warp] = b; }
+    acc_sum = 0.0f; acc_sq = 0.0f; acc_max = -INFINITY;
+  };
   auto write_stats = [&]() {
     if (warp != 0 || pending_stats < 0) return;
     float a, b;
@@ -334,6 +345,7 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
 
   for (int buf = 0; item < n_items; item += gridDim.x, buf ^= 1) {
     const int clip = clip0 + item / tiles_per_clip, tile = item % tiles_per_clip;
+    reduce_warp_stats();
     cp_async_wait_all();
     __syncthreads();  // this tile's samples have landed; the previous tile's power rows (other slot), output tile and red[] are complete
     if (kNorm != YOHO_NORM_NONE) write_stats();
@@ -465,7 +477,6 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
     __syncthreads();
     // ---- log10, per-tile statistics and the stores: the tile's (frames, n_mels) block is contiguous in `out` -----------
     {
-      float acc_sum = 0.0f, acc_sq = 0.0f, acc_max = -INFINITY;
       auto finish = [&](float v, bool valid) {
         if (kNorm == YOHO_NORM_NONE) return v;
         v = lg2_approx(fmaxf(v, log_floor)) * 0.30102999566398120f;      // the floor keeps the argument normal
@@ -499,16 +510,13 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
         for (int f = warp; f < rows; f += kWarps)
           for (int m = lane; m < n_mels; m += 32) out_tile[f * n_mels + m] = finish(otile[m * kFramesPerCta + f], true);
       }
-      if (kNorm != YOHO_NORM_NONE) {
-        // per-warp partials now, the cross-warp sum after the next barrier (top of the loop / after it): fixed order, no atomics
-        const float a = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sum) : warp_max(acc_max);
-        const float b = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sq) : 0.0f;
-        if (lane == 0) { sm.red[warp] = a; sm.red[32 + warp] = b; }
-        pending_stats = clip * tiles_per_clip + tile;
-      }
+      // per-thread partials stay in registers; warp sums at the top of the next iteration, the cross-warp sum after its
+      // first barrier: fixed order, no atomics
+      if (kNorm != YOHO_NORM_NONE) pending_stats = clip * tiles_per_clip + tile;
     }
   }
   if (kNorm != YOHO_NORM_NONE) {
+    reduce_warp_stats();
     __syncthreads();
     write_stats();
   }
