@@ -1,6 +1,6 @@
 #!/bin/bash
 # round 2, call B: full GPU suite + smoke + every BASELINE config's bench line on the final code
-tag=${1:-r02c}
+tag=${1:-r02d}
 mkdir -p gpurun_out
 rm -f gpurun_out/r02_parity.txt
 echo "===== pytest -m gpu ====="
