@@ -183,7 +183,7 @@ extern "C" int yoho_filterbank_create(yoho_ctx* ctx, const float* host_filters, 
   // |2 X[k]|^2 comes out of the packed-pair FFT; stft scales by 1/sum(w) (scaling='spectrum').
   const double scale = 0.25 / (ctx->window_sum * ctx->window_sum);
   // Groups of eight bands (longest first) share one trip count: one warp-round of the kernel's mel phase.  The groups are
-  // dealt to the CTA's five warps longest-processing-time first and stored [round][warp]; a warp without a group in a round
+  // dealt to the CTA's six warps longest-processing-time first and stored [round][warp]; a warp without a group in a round
   // finds a filler (trip 0).
   const int n_real = (n_mels + kMelGroup - 1) / kMelGroup;
   std::vector<int> trips(n_real);

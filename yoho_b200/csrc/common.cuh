@@ -106,8 +106,8 @@ constexpr int kMelMaxBands = 128;      // n_mels <= 128 (band pairs * 2)
 constexpr int kMelMaxWeights = 600;    // (w, w) entries held in shared memory: sum over bands of their pair's trip
 constexpr int kMelBins = 201;          // n_fft / 2 + 1
 constexpr int kMelGroup = 8;           // bands that share a trip count: one warp-round of the mel phase (4 lane slots x 2)
-constexpr int kMelWarps = 5;           // warps of the frontend CTA: the host lays the groups out as [round][warp]
-constexpr int kMelMaxRounds = 6;       // rounds x kMelWarps schedule entries (32 bytes of shared memory)
+constexpr int kMelWarps = 6;           // warps of the frontend CTA: the host deals the band groups to them
+constexpr int kMelMaxRounds = 5;       // rounds x kMelWarps schedule entries (32 bytes of shared memory)
 struct yoho_filterbank {
   int device = -1;
   int n_mels = 0, n_bins = 0;

@@ -56,8 +56,10 @@ constexpr int kHop = 160;
 constexpr int kBins = kMelBins;                                   // 201
 constexpr int kFramesPerCta = 32;
 constexpr int kFftsPerCta = kFramesPerCta / 2;                    // 16
-constexpr int kThreads = 160;                                     // 10 column-pair tasks x 16 FFTs
-constexpr int kWarps = kThreads / 32;                             // 5
+constexpr int kFftThreads = 160;                                  // 10 column-pair tasks x 16 FFTs
+constexpr int kThreads = 192;                                     // + one warp: columns 0 / 10 of pass 2 on their own warp, and 2 x 6
+constexpr int kWarps = kThreads / 32;                             //   warps per SM are three per scheduler (2 x 5 left two schedulers with three
+                                                                  //   warps and two with two: the warps of the crowded ones were late at every barrier)
 constexpr int kTileSamples = (kFramesPerCta - 1) * kHop + kNfft;  // 5360
 constexpr int kEBlockRows = 21;                                   // rows per k1 block of E: 20 + 1 so that neighbouring blocks differ in row parity
 constexpr int kERows = 20 * kEBlockRows;                          // 420 rows of 16 floats (one per FFT)
@@ -203,7 +205,9 @@ __device__ __forceinline__ void stage_pcm_async(T* dst, const T* __restrict__ pc
   constexpr int kChunksPerBlock = 320 / kVec;   // a chunk never straddles a 320-sample block
   static_assert(kTileSamples % kVec == 0 && 320 % kVec == 0, "chunking");
   const T* clip = pcm + clip_off;
+  constexpr int kThreads = kFftThreads;         // the copy pattern is laid out for 160 threads; the sixth warp takes no part
   static_assert(kThreads % kChunksPerBlock == 0, "a thread's chunks advance by whole 320-sample blocks");
+  if (threadIdx.x >= kThreads) return;
   if (vec_ok && s0 + kTileSamples <= valid) {
     // interior tile: chunk c = tid + it * kThreads lands at c * kVec + kVec * (c / kChunksPerBlock); both advance by constants
     T* d = dst + threadIdx.x * kVec + kVec * (threadIdx.x / kChunksPerBlock);
@@ -292,7 +296,11 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
   const int warp = tid >> 5, lane = tid & 31;
   // FFT roles: half warp hw holds FFTs 8 hw .. 8 hw + 7, each twice: sub = 0 / 1 are the warp's two column-pair tasks
   const int fft = (lane & 7) + 8 * (lane >> 4);
-  const int task = 2 * warp + ((lane >> 3) & 1);          // pass 1: columns 2 task, 2 task + 1; pass 2: columns task, 20 - task
+  const int sub = (lane >> 3) & 1;
+  const int task = 2 * warp + sub;                        // pass 1 (warps 0-4): columns 2 task, 2 task + 1
+  // pass 2: columns task2, 20 - task2; columns 0 and 10 (task2 = 0, their own partners: a different untangle) belong to the
+  // sixth warp, so that no warp runs both untangle variants one after the other; -1 = this half warp rests
+  const int task2 = warp == kWarps - 1 ? (sub == 0 ? 0 : -1) : (task == 0 ? -1 : task);
   // mel roles: half warp h takes band h of the warp's current band pair, lane = frame pair
   const float log_floor = (kNorm == YOHO_NORM_WHISPER) ? 1e-10f : 1e-13f;
   constexpr int kWin = sizeof(T) == 2 ? 1 : 0;
@@ -354,7 +362,7 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
 
     C2 v[20];
     // ---- pass 1: columns n2 = 2 task, 2 task + 1; DFT over n1 of x[20 n1 + n2], frames A / B as re / im ------------------
-    {
+    if (warp < kFftThreads / 32) {
       const T* src = reinterpret_cast<const T*>(sm.slot[buf]) + fft * Smem::kFftStride + 2 * task;
       uint64_t r[28];          // rows 0..19 are frame A; frame B starts 160 samples = 8 rows later
 #pragma unroll
@@ -392,8 +400,9 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
       }
     }
     __syncthreads();
-    // ---- pass 2: columns (task, 20 - task) [task 0: columns 0 and 10] in the two slots; DFT over n2 ----------------------
-    {
+    // ---- pass 2: columns (task2, 20 - task2) [task2 0: columns 0 and 10] in the two slots; DFT over n2 -------------------
+    if (task2 >= 0) {
+      const int task = task2;                                 // shadows the pass-1 role
       const int bx = task, by = task == 0 ? 10 : 20 - task;
 #pragma unroll
       for (int n2 = 0; n2 < 20; ++n2) {
@@ -448,7 +457,7 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
         const uint32_t odd = uint32_t(band.y & 1) << 6, row = pbase + uint32_t(band.y) * (kPRow * 4);
         return MelBandAddr{row + (col ^ odd), row + (kPRow * 4) + (col ^ odd ^ 64u), wbase + uint32_t(band.z) * 8u};
       };
-      // the host has dealt the groups to the five warps (longest processing time first): schedule[round][warp]
+      // the host has dealt the groups to the six warps (longest processing time first): schedule[round][warp]
       for (int round = 0; round < n_rounds; ++round) {
         const int group = sm.mel_sched[round * kWarps + warp];
         if (group < 0) continue;
