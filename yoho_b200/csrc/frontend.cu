@@ -33,6 +33,9 @@
 //     applied with lane = (four frames, band slot): a warp walks a group of eight bands per round (packed FMA on two frame
 //     pairs, 128-bit loads), the groups dealt to the warps by the host; the (32 frames x n_mels) result is transposed
 //     through shared memory so the global stores are full 128-byte lines.
+//   * Six warps per CTA: five carry the ten column-pair tasks of the two passes, the sixth owns columns 0 and 10 of pass 2
+//     (their own partners: a different untangle, which would otherwise make one warp run both variants in turn) and a share
+//     of the mel groups; two CTAs per SM are twelve warps, three per scheduler.
 //   * Persistent CTAs (two per SM) walk the (clip, tile) list; the PCM of the next tile arrives by 16-byte zero-filling
 //     cp.async into the other slot while the current tile is transformed (int16 is converted when it is read).
 #include "common.cuh"
