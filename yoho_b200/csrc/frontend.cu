@@ -92,7 +92,6 @@ struct FrontendSmem {
   alignas(16) float2 mel_w[kMelMaxWeights];   // (w, w) per walked bin (resident for the whole kernel)
   int4 mel_band[kMelMaxBands];
   signed char mel_sched[32];                  // [round][warp] -> group or -1
-  float red[2 * 32];
 };
 static_assert(kFramesPerCta * kMelMaxBands * 4 <= kERows * kFftsPerCta * 4, "the output tile overlays e_re");
 static_assert(kWarps == kMelWarps, "the filterbank's [round][warp] layout is built for this CTA");
@@ -328,38 +327,32 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
   for (int i = tid; i < kMelGroup * n_groups; i += kThreads) sm.mel_band[i] = __ldg(fb_bands + i);
   if (tid < 32) sm.mel_sched[tid] = static_cast<signed char>(__ldg(reinterpret_cast<const int*>(fb_bands + kMelGroup * n_groups) + tid));
 
-  // statistics of the tile finished last: every thread carries its partial sums into the next iteration, where the warp
-  // reduction (a chain of five dependent shuffles, 6 % of the kernel's stall samples when it sat at the end of the output
-  // phase) runs before the first barrier, i.e. where the warps wait for the slowest one anyway; warp 0 adds the per-warp
-  // partials from red[] once that barrier has passed
+  // Statistics of the tile finished last.  Every thread leaves its partial {sum, sum of squares} (or {max}) in the tail of
+  // the tile's slot (the power rows there are dead after the mel phase and the next staging only writes the PCM part);
+  // after the next iteration's first barrier the sixth warp, which has no column pair in pass 1, adds the 192 partials in a
+  // fixed order and writes the tile's entry.  No shuffle chain on the five FFT warps (it held 6 % of the stall samples).
+  constexpr int kPartOffset = Smem::kSlotBytes - kThreads * int(sizeof(float2));
+  static_assert(kPartOffset >= int(Smem::kRawElems * sizeof(T)) && kPartOffset % 8 == 0, "the partials sit behind the staged samples");
   int pending_stats = -1;
-  float acc_sum = 0.0f, acc_sq = 0.0f, acc_max = -INFINITY;
-  auto reduce_warp_stats = [&]() {
-    if (kNorm == YOHO_NORM_NONE || pending_stats < 0) return;
-    const float a = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sum) : warp_max(acc_max);
-    const float b = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(acc_sq) : 0.0f;
-    if (lane == 0) { sm.red[warp] = a; sm.red[32 + warp] = b; }
-    acc_sum = 0.0f; acc_sq = 0.0f; acc_max = -INFINITY;
-  };
-  auto write_stats = [&]() {
-    if (warp != 0 || pending_stats < 0) return;
-    float a, b;
-    if (kNorm == YOHO_NORM_REFERENCE) {
-      a = warp_sum(lane < kWarps ? sm.red[lane] : 0.0f);
-      b = warp_sum(lane < kWarps ? sm.red[32 + lane] : 0.0f);
-    } else {
-      a = warp_max(lane < kWarps ? sm.red[lane] : -INFINITY);
-      b = 0.0f;
+  auto collect_stats = [&](int slot_of_tile) {
+    if (kNorm == YOHO_NORM_NONE || warp != kWarps - 1 || pending_stats < 0) return;
+    const float2* part = reinterpret_cast<const float2*>(sm.slot[slot_of_tile] + kPartOffset);
+    float a = (kNorm == YOHO_NORM_REFERENCE) ? 0.0f : -INFINITY, b = 0.0f;
+#pragma unroll
+    for (int i = 0; i < kThreads / 32; ++i) {
+      const float2 v = part[lane + 32 * i];
+      if (kNorm == YOHO_NORM_REFERENCE) { a += v.x; b += v.y; } else a = fmaxf(a, v.x);
     }
+    a = (kNorm == YOHO_NORM_REFERENCE) ? warp_sum(a) : warp_max(a);
+    if (kNorm == YOHO_NORM_REFERENCE) b = warp_sum(b);
     if (lane == 0) stats[pending_stats] = make_float2(a, b);
   };
 
   for (int buf = 0; item < n_items; item += gridDim.x, buf ^= 1) {
     const int clip = clip0 + item / tiles_per_clip, tile = item % tiles_per_clip;
-    reduce_warp_stats();
     cp_async_wait_all();
-    __syncthreads();  // this tile's samples have landed; the previous tile's power rows (other slot), output tile and red[] are complete
-    if (kNorm != YOHO_NORM_NONE) write_stats();
+    __syncthreads();  // this tile's samples have landed; the previous tile's power rows (other slot), output tile and partials are complete
+    collect_stats(buf ^ 1);
     if (item + int(gridDim.x) < n_items) stage(item + gridDim.x, buf ^ 1);
     cp_async_commit();
 
@@ -489,6 +482,7 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
     __syncthreads();
     // ---- log10, per-tile statistics and the stores: the tile's (frames, n_mels) block is contiguous in `out` -----------
     {
+      float acc_sum = 0.0f, acc_sq = 0.0f, acc_max = -INFINITY;
       auto finish = [&](float v, bool valid) {
         if (kNorm == YOHO_NORM_NONE) return v;
         v = lg2_approx(fmaxf(v, log_floor)) * 0.30102999566398120f;      // the floor keeps the argument normal
@@ -522,15 +516,16 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
         for (int f = warp; f < rows; f += kWarps)
           for (int m = lane; m < n_mels; m += 32) out_tile[f * n_mels + m] = finish(otile[m * kFramesPerCta + f], true);
       }
-      // per-thread partials stay in registers; warp sums at the top of the next iteration, the cross-warp sum after its
-      // first barrier: fixed order, no atomics
-      if (kNorm != YOHO_NORM_NONE) pending_stats = clip * tiles_per_clip + tile;
+      if (kNorm != YOHO_NORM_NONE) {
+        reinterpret_cast<float2*>(sm.slot[buf] + kPartOffset)[tid] =
+            make_float2(kNorm == YOHO_NORM_REFERENCE ? acc_sum : acc_max, kNorm == YOHO_NORM_REFERENCE ? acc_sq : 0.0f);
+        pending_stats = clip * tiles_per_clip + tile;
+      }
     }
-  }
-  if (kNorm != YOHO_NORM_NONE) {
-    reduce_warp_stats();
-    __syncthreads();
-    write_stats();
+    if (item + int(gridDim.x) >= n_items && kNorm != YOHO_NORM_NONE) {   // the CTA's last tile: nobody comes back to the top
+      __syncthreads();
+      collect_stats(buf);
+    }
   }
 }
 
