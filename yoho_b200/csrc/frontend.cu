@@ -671,11 +671,15 @@ static int frames_of(int n_samples, int n_fft, int hop) {
 
 static int logmel_tiles(int frames) { return ceil_div(frames, kFramesPerCta); }
 
-// Clips per launch pair: keep one chunk's log-mel (written by logmel_kernel, rewritten in place by
-// normalize_apply_kernel) well inside the 126 MB L2 so the second pass costs no DRAM traffic.
+// Clips per launch pair.  Round 1 kept one chunk's log-mel (written by logmel_kernel, rewritten in place by
+// normalize_apply_kernel) inside the L2 (48 MB chunks); with the round-2 kernel the launch tails of five chunks cost more
+// than the DRAM traffic of an unchunked second pass (256 clips in the step: 0.68 + 0.12 ms chunked, 0.63 + 0.10 ms in
+// one launch pair), so the default is one launch pair per call.  YOHO_LOGMEL_CHUNK_MB (read once) restores chunking for A/B.
 static int clips_per_chunk(int frames, int n_mels) {
+  static const size_t chunk_mb = [] { const char* e = getenv("YOHO_LOGMEL_CHUNK_MB"); long v = e ? atol(e) : 0; return size_t(v > 0 ? v : 0); }();
+  if (chunk_mb == 0) return 65535;
   size_t per_clip = size_t(frames) * n_mels * sizeof(float);
-  size_t c = (48u << 20) / (per_clip ? per_clip : 1);
+  size_t c = (chunk_mb << 20) / (per_clip ? per_clip : 1);
   return int(c < 1 ? 1 : (c > 65535 ? 65535 : c));
 }
 
