@@ -173,3 +173,74 @@ def test_chunked_long_recording_ingest(api, dtype):
     assert short[0, 7].max() <= 1e-12 * short[0, 6].max()
     with pytest.raises(ValueError):
         api.log_mel_spectogram_chunked(rec.reshape(1, -1), clip_samples=clip)
+
+
+# ------------------------------------------------------------------ the band packer and the mel phase on arbitrary filterbanks
+def _custom_bank(kind: str, n_mels: int, rng) -> np.ndarray:
+    """(n_mels, 201) float32 banks that stress yoho_filterbank_create: empty bands, one-bin bands, bands touching bin 0 and
+    bin 200, bands longer than one chunk of four steps, heavy overlap, any number of bands (groups of eight + a remainder)."""
+    bank = np.zeros((n_mels, 201), np.float32)
+    for m in range(n_mels):
+        if kind == "random":
+            # many bands must be short ones: the kernel's weight tile holds 600 walked bins (groups of eight, padded)
+            length = int(rng.choice([0, 1, 2, 3, 5, 8, 9, 14, 17, 23] if n_mels <= 48 else [0, 1, 1, 2, 2, 3, 3, 4, 5, 7]))
+            lo = int(rng.integers(0, 201 - length + 1)) if length else 0
+        elif kind == "edges":                                    # alternately glued to the first and the last bin
+            length = 1 + m % 11
+            lo = 0 if m % 2 == 0 else 201 - length
+        else:                                                    # "wide": every band 20..40 bins, sliding over the spectrum
+            length = 20 + (m * 7) % 21
+            lo = (m * 13) % (201 - length + 1)
+        if length:
+            bank[m, lo:lo + length] = rng.uniform(0.05, 1.0, length).astype(np.float32)
+            if length > 2 and m % 3 == 0:
+                bank[m, lo + 1] = 0.0                            # a hole inside the band: still one contiguous walk
+    return bank
+
+
+@pytest.mark.parametrize("kind,n_mels", [("random", 1), ("random", 7), ("random", 8), ("random", 9), ("random", 40), ("random", 64),
+                                         ("random", 100), ("random", 127), ("random", 128), ("edges", 33), ("edges", 80),
+                                         ("wide", 5), ("wide", 12)])
+def test_arbitrary_filterbanks_through_the_c_abi(api, kind, n_mels):
+    """yoho_filterbank_create sorts the bands by length, packs them in groups of eight with a common trip count and deals
+    the groups to the kernel's six warps; the mel phase walks them four frames per thread.  Any dense (n_mels, 201) matrix
+    must come out as the plain matrix product with the power spectrum (audio.py:36), whatever its band structure."""
+    import ctypes as C
+    import torch
+    from oracle import frontend as fo
+    from yoho_b200._lib import NORM_NONE, check
+    from yoho_b200.runtime import get_runtime
+    from yoho_b200.synth import synth_batch
+    rng = np.random.default_rng(1000 * n_mels + len(kind))
+    bank = _custom_bank(kind, n_mels, rng)
+    rt = get_runtime()
+    fb = rt.filterbank(bank)
+    B, N = 2, 20333                                             # 4 tiles per clip, ragged last tile
+    x = synth_batch(B, N)
+    frames = rt.lib.yoho_stft_frames(N, 400, 160)
+    pcm = torch.from_numpy(x).cuda()
+    out = torch.full((B, frames, n_mels), float("nan"), device="cuda")
+    ws_bytes = rt.lib.yoho_logmel_workspace_bytes(B, N, 400, 160, n_mels)
+    ws = rt.workspace("logmel", ws_bytes)
+    check(rt.lib.yoho_logmel_f32(rt.ctx, fb, C.c_void_p(pcm.data_ptr()), B, N, 400, 160, C.c_void_p(out.data_ptr()), NORM_NONE,
+                                 C.c_void_p(rt.aligned_ptr(ws)), ws_bytes, rt.stream_ptr()))
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    want = fo.mel_spectogram(x.astype(np.float64), 400, 160, 16000, n_mels, filters=bank)
+    assert got.shape == want.shape and np.isfinite(got).all()
+    empty = ~bank.any(axis=1)
+    assert np.array_equal(got[..., empty], np.zeros_like(got[..., empty]))          # an all-zero band gives exact zeros
+    scale = np.abs(want).max(axis=-1, keepdims=True)
+    assert np.all(np.abs(got - want) <= 2.3e-4 * np.abs(want) + 2e-6 * scale + 1e-12)
+
+
+def test_filterbank_limits_are_reported(api):
+    """More walked bins than the kernel's weight tile holds is an error with a message, not a wrong answer."""
+    import ctypes as C
+    from yoho_b200._lib import YohoError, check
+    from yoho_b200.runtime import get_runtime
+    rt = get_runtime()
+    bank = np.ones((16, 201), np.float32)                        # sixteen bands over the whole spectrum
+    handle = C.c_void_p()
+    with pytest.raises(YohoError, match="weight tile|band of"):
+        check(rt.lib.yoho_filterbank_create(rt.ctx, bank.ctypes.data_as(C.c_void_p), 16, 201, C.byref(handle)))

@@ -459,9 +459,8 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
         if (group < 0) continue;
         const int4 bx = sm.mel_band[kMelGroup * group + slot], by = sm.mel_band[kMelGroup * group + 4 + slot];
         int steps = bx.w >> 1;                                  // two bins a step; the same for the eight bands of the group
-        if (steps == 0) continue;
         MelBandAddr ax = address(bx), ay = address(by);
-        uint64_t sum_x[2] = {0ull, 0ull}, sum_y[2] = {0ull, 0ull};
+        uint64_t sum_x[2] = {0ull, 0ull}, sum_y[2] = {0ull, 0ull};   // a group of empty bands (no steps) still stores its zeros
         // one straight-line variant per step count up to four; longer bands take chunks of four steps first
         while (steps > 4) {
           mel_oct<4>(ax, ay, sum_x, sum_y);
@@ -470,6 +469,7 @@ logmel_kernel(const T* __restrict__ pcm, int n_samples, long long total_samples,
           steps -= 4;
         }
         switch (steps) {
+          case 0: break;
           case 1: mel_oct<1>(ax, ay, sum_x, sum_y); break;
           case 2: mel_oct<2>(ax, ay, sum_x, sum_y); break;
           case 3: mel_oct<3>(ax, ay, sum_x, sum_y); break;
