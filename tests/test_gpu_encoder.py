@@ -400,3 +400,27 @@ def test_ab_switches_still_match_the_oracle(rt, switch):
     r = subprocess.run([sys.executable, str(root / "tools" / "sanitize_case.py")], env=env, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "[sanitize] done" in r.stdout
+
+
+@pytest.mark.parametrize("n_mels,dims,heads,layers,frames,batch", [(80, 128, 2, 2, 41, 3), (80, 128, 2, 3, 199, 5), (128, 192, 3, 2, 777, 2),
+                                                                   (96, 256, 4, 1, 1023, 1), (80, 320, 5, 2, 130, 7), (64, 64, 1, 2, 3, 2),
+                                                                   (80, 448, 7, 1, 257, 3)])
+def test_ragged_encoder_shapes_vs_oracle(rt, n_mels, dims, heads, layers, frames, batch):
+    """Shapes no BASELINE config has: row counts that are not multiples of the 128-row GEMM tile (ragged last tile of the
+    LayerNorm-producer epilogues: residual rows fetched and stored by TMA past the end), sequences shorter than one 64-key
+    attention step, odd head counts, widths that are not multiples of 256, mel counts 64 / 96 / 128 in the Conv_0 taps.
+    Both compute paths against the float64 oracle (whisper.py:117-135)."""
+    from oracle import encoder as eo
+    from yoho_b200.nn import AudioEncoder, init_encoder_params
+    params = init_encoder_params(n_mels, dims, layers, seed=frames)
+    rng = np.random.default_rng(frames + batch)
+    mel = rng.standard_normal((batch, frames, n_mels)).astype(np.float32)
+    T = eo.conv_out_len(frames)
+    want = eo.audio_encoder(params, mel.astype(np.float64), heads, np.float64)
+    model = AudioEncoder(T, dims, heads, layers)
+    out32 = model.apply({"params": params}, mel, compute="fp32")
+    assert out32.shape == want.shape == (batch, T, dims)
+    assert np.abs(out32 - want).max() <= 1e-4 * max(1.0, float(np.abs(want).max()))
+    out16 = model.apply({"params": params}, mel, compute="bf16")
+    assert np.isfinite(out16).all()
+    assert np.abs(out16 - want).max() / np.abs(want).max() <= 2e-2
