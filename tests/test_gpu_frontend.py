@@ -256,3 +256,24 @@ def test_filterbank_limits_are_reported(api):
     handle = C.c_void_p()
     with pytest.raises(YohoError, match="weight tile|band of"):
         check(rt.lib.yoho_filterbank_create(rt.ctx, bank.ctypes.data_as(C.c_void_p), 16, 201, C.byref(handle)))
+
+
+@pytest.mark.parametrize("n_samples", [401, 560, 561, 5360, 5361, 5519, 5520, 10480, 10481])
+def test_lengths_at_tile_and_frame_boundaries(api, n_samples):
+    """Clip lengths that end exactly on / one sample past a frame (hop 160) and a 32-frame tile (5360 + 5120 k samples):
+    the tail frame is zero padded (audio.py:33 `padded=True`), the last tile is ragged, the statistics cover real frames only."""
+    from oracle import frontend as fo
+    from yoho_b200.synth import synth_batch
+    x = synth_batch(3, n_samples)
+    _, frames = fo.stft_geometry(n_samples, 400, 160)
+    want = fo.mel_spectogram(x.astype(np.float64), 400, 160, 16000, 80)
+    got = api.mel_spectogram(x, 400, 160, 16000, 80)
+    assert got.shape == want.shape == (3, frames, 80)
+    scale = np.abs(want).max(axis=-1, keepdims=True)
+    assert np.all(np.abs(got - want) <= 2.3e-4 * np.abs(want) + 2e-6 * scale + 1e-12)
+    for norm, mode in (("reference", fo.NORM_REFERENCE), ("whisper", fo.NORM_WHISPER)):
+        out = api.log_mel_spectogram(x, n_mels=80, norm=norm)
+        ref = fo.log_mel(x, n_mels=80, norm_mode=mode)
+        posed = want > 1e-6 * scale
+        assert np.abs(out - ref)[posed].max() <= TOL, (norm, np.abs(out - ref)[posed].max())
+        assert np.mean(np.abs(out - ref) > 1e-3) <= 1e-3
